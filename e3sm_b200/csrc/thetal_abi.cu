@@ -1,0 +1,744 @@
+// C ABI of libthetal_b200.so: host-side session, device-resident state, step sequencing.
+// Mirrors the HOMMEXX C interface the Fortran theta-l_kokkos driver binds
+// (H/src/theta-l_kokkos/theta_f2c_mod.F90, impl cxx/cxx_f90_interface_theta.cpp,
+//  H/src/share/cxx/prim_driver.cpp, mpi/mpi_cxx_f90_interface.cpp); see include/thetal_b200.h.
+#include "../../include/thetal_b200.h"
+#include "thetal_kernels.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <array>
+#include <cmath>
+
+using namespace thetal;
+
+namespace {
+
+struct Connection { int e1, dir1, e2_lid, e2_gid, e2_pid, dir2; };
+
+struct Session {
+  bool active = false;
+  int rank = 0, nranks = 1, device = 0;
+  int abort_on_error = 1;
+  int last_error = 0;
+  std::string last_msg;
+  Params prm{};
+  bool params_set = false;
+  int nlev = 0;
+  int nm1 = 0, n0 = 1, np1 = 2, nstep = 0, nstep0 = 0;   // 0-based
+  int hypervis_order = 2;
+  double hypervis_scaling = 0, laplace_scaling = 0;
+  // hvcoord
+  std::vector<double> hyam, hyai, hybm, hybi, dp0, nu_scale_top;
+  double dvv[16], mp[16];
+  // connectivity
+  int max_corner = 1;
+  std::vector<Connection> conns;
+  // host staging of geometry (filled per element, uploaded in init_functors_c)
+  std::vector<double> hD, hDinv, hmetdet, hrmetdet, hspheremp, hrspheremp, hfcor, hphis, hmetinv,
+      htensorvisc, hvec, hgradphis;
+  std::vector<int> hdss;
+  // device
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::vector<void *> allocs;
+  StatePtrs tl[NTL]{}, tensA{}, tensB{};
+  Geo geo{};
+  Derived der{};
+  RefStates ref{};
+  int *d_err = nullptr, *d_maxiter = nullptr;
+  unsigned long long *d_maxdelta = nullptr;
+  bool device_ready = false;
+  long launches = 0;
+  // DIRK statistics (element_state.F90:20-22)
+  int max_itercnt = 0;
+  double max_deltaerr = 0;
+};
+
+Session S;
+
+void fail(int code, const std::string &msg)
+{
+  S.last_error = code;
+  S.last_msg = msg;
+  fprintf(stderr, "thetal_b200: ERROR %d: %s\n", code, msg.c_str());
+  if (S.abort_on_error) abort();
+}
+
+#define CUDA_OK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fail(100, std::string(#x) + ": " + cudaGetErrorString(e_)); } } while (0)
+
+template <class T> T *dalloc(size_t n)
+{
+  void *p = nullptr;
+  CUDA_OK(cudaMalloc(&p, n * sizeof(T)));
+  CUDA_OK(cudaMemset(p, 0, n * sizeof(T)));
+  S.allocs.push_back(p);
+  return (T *)p;
+}
+
+StatePtrs alloc_state(int nelem, int nlev)
+{
+  StatePtrs s;
+  s.v = dalloc<double>((size_t)nelem * 32 * nlev);
+  s.w = dalloc<double>((size_t)nelem * 16 * (nlev + 1));
+  s.th = dalloc<double>((size_t)nelem * 16 * nlev);
+  s.phi = dalloc<double>((size_t)nelem * 16 * (nlev + 1));
+  s.dp = dalloc<double>((size_t)nelem * 16 * nlev);
+  return s;
+}
+
+void require(bool cond, const char *what)
+{
+  if (!cond) fail(2, std::string("precondition failed: ") + what);
+}
+
+// Errors::check_option equivalents (cxx_f90_interface_theta.cpp:57-73)
+void check_in(const char *name, int v, std::initializer_list<int> ok)
+{
+  for (int o : ok) if (o == v) return;
+  fail(3, std::string("init_simulation_params_c: unsupported value for ") + name + ": " + std::to_string(v));
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------- session / comm
+void initialize_hommexx_session(void)
+{
+  if (S.active) return;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) { fail(1, "no CUDA device: libthetal_b200 has no CPU fallback"); return; }
+  CUDA_OK(cudaSetDevice(S.device % ndev));
+  CUDA_OK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
+  CUDA_OK(cudaEventCreate(&S.ev0));
+  CUDA_OK(cudaEventCreate(&S.ev1));
+  S.active = true;
+}
+
+void finalize_hommexx_session(void)
+{
+  if (!S.active) return;
+  cudaDeviceSynchronize();
+  for (void *p : S.allocs) cudaFree(p);
+  S.allocs.clear();
+  if (S.ev0) cudaEventDestroy(S.ev0);
+  if (S.ev1) cudaEventDestroy(S.ev1);
+  if (S.stream) cudaStreamDestroy(S.stream);
+  const int dev = S.device, rank = S.rank, nranks = S.nranks, aoe = S.abort_on_error;
+  S = Session();
+  S.device = dev; S.rank = rank; S.nranks = nranks; S.abort_on_error = aoe;
+}
+
+void reset_cxx_comm(const int *f_comm) { (void)f_comm; }
+
+void thetal_b200_init_comm(const int *rank, const int *nranks, const int *device, const void *nccl_id)
+{
+  S.rank = *rank; S.nranks = *nranks; S.device = *device;
+  (void)nccl_id;
+  if (S.nranks > 1) fail(4, "multi-rank halo exchange is not built in this round (replicas only)");
+}
+void thetal_b200_get_nccl_id(void *out) { memset(out, 0, 128); }
+void thetal_b200_set_abort_on_error(const int *flag) { S.abort_on_error = *flag; }
+int thetal_b200_last_error(void) { return S.last_error; }
+const char *thetal_b200_last_error_msg(void) { return S.last_msg.c_str(); }
+void thetal_b200_set_nlev(const int *nlev)
+{
+  if (*nlev < 2 || *nlev > 128) { fail(3, "nlev must be in [2,128]"); return; }
+  S.nlev = *nlev;
+}
+void thetal_b200_set_extra_params(const int *unused, const int *nlev_tom)
+{
+  (void)unused;
+  S.prm.nlev_tom = *nlev_tom;
+}
+
+// ---------------------------------------------------------------- connectivity
+void init_connectivity(const int *num_local_elems, const int *max_corner_elems)
+{
+  S.conns.clear();
+  S.max_corner = *max_corner_elems;
+  S.conns.reserve((size_t)*num_local_elems * 8);
+}
+
+void add_connection(const int *e1_lid, const int *e1_gid, const int *e1_pos, const int *e1_pid,
+                    const int *e2_lid, const int *e2_gid, const int *e2_pos, const int *e2_pid)
+{
+  require(*e1_lid >= 1 && *e1_gid >= 1 && *e1_pos >= 1 && *e1_pid >= 1 && *e2_lid >= 1 && *e2_gid >= 1 &&
+          *e2_pos >= 1 && *e2_pid >= 1, "add_connection: F90 indices should start at 1");
+  Connection c;
+  c.e1 = *e1_lid - 1;
+  c.dir1 = *e1_pos / S.max_corner - 1;      // W=0,E=1,S=2,N=3,SW=4,SE=5,NW=6,NE=7
+  c.e2_lid = *e2_lid - 1; c.e2_gid = *e2_gid - 1; c.e2_pid = *e2_pid - 1;
+  c.dir2 = *e2_pos / S.max_corner - 1;
+  (void)e1_gid;
+  if (*e1_pid - 1 == S.rank) S.conns.push_back(c);
+}
+
+static void edge_points(int dir, int pts[4])
+{ // natural ordering of the dofs of an edge (ConnectivityHelpers.hpp:30-47)
+  for (int k = 0; k < 4; k++) {
+    switch (dir) {
+      case 0: pts[k] = 4 * k; break;          // W: i=0
+      case 1: pts[k] = 4 * k + 3; break;      // E: i=3
+      case 2: pts[k] = k; break;              // S: j=0
+      default: pts[k] = 12 + k; break;        // N: j=3
+    }
+  }
+}
+static int corner_point(int dir) { return dir == 4 ? 0 : dir == 5 ? 3 : dir == 6 ? 12 : 15; }
+
+void finalize_connectivity(void)
+{
+  const int nelem = S.prm.nelem;
+  require(nelem > 0, "init_elements_c must precede finalize_connectivity");
+  // slot[e][p]: contributions by kind: 0..3 = W,E,S,N edge, 4 = corner
+  std::vector<std::array<int, 5>> by_kind((size_t)nelem * 16);
+  for (auto &a : by_kind) a.fill(-1);
+  for (const Connection &c : S.conns) {
+    if (c.e2_pid != S.rank) { fail(4, "remote connection: multi-rank halo exchange is not built in this round"); return; }
+    if (c.dir1 < 4) {
+      require(c.dir2 < 4, "edge connected to corner");
+      int p1[4], p2[4];
+      edge_points(c.dir1, p1); edge_points(c.dir2, p2);
+      // orientation (ConnectivityHelpers.hpp:64-67): same-side pairs and W/N, E/S are reversed
+      const int a = c.dir1, b = c.dir2;
+      const bool rev = (a == b) || (a == 0 && b == 3) || (a == 3 && b == 0) || (a == 1 && b == 2) || (a == 2 && b == 1);
+      for (int k = 0; k < 4; k++)
+        by_kind[(size_t)c.e1 * 16 + p1[k]][c.dir1] = c.e2_lid * 16 + p2[rev ? 3 - k : k];
+    } else {
+      by_kind[(size_t)c.e1 * 16 + corner_point(c.dir1)][4] = c.e2_lid * 16 + corner_point(c.dir2);
+    }
+  }
+  // unpack order of edge_mod.F90:888-941: per i: S,N,W,E ; so SW: S,W  SE: E,S  NW: N,W  NE: N,E ; corners last
+  S.hdss.assign((size_t)nelem * 48, -1);
+  for (int e = 0; e < nelem; e++)
+    for (int p = 0; p < 16; p++) {
+      const auto &k = by_kind[(size_t)e * 16 + p];
+      int order[5];
+      if (p == 3) { order[0] = 1; order[1] = 2; order[2] = 0; order[3] = 3; }          // SE: E,S
+      else { order[0] = 2; order[1] = 3; order[2] = 0; order[3] = 1; }                  // S,N,W,E
+      order[4] = 4;
+      int n = 0;
+      for (int j = 0; j < 5; j++)
+        if (k[order[j]] >= 0) { require(n < 3, "more than 3 DSS neighbours at a point"); S.hdss[((size_t)e * 16 + p) * 3 + n++] = k[order[j]]; }
+    }
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// ---------------------------------------------------------------- parameters
+void init_simulation_params_c(const int *remap_alg, const int *limiter_option, const int *rsplit,
+    const int *qsplit, const int *time_step_type, const int *qsize, const int *state_frequency,
+    const double *nu, const double *nu_p, const double *nu_q, const double *nu_s,
+    const double *nu_div, const double *nu_top, const int *hypervis_order,
+    const int *hypervis_subcycle, const int *hypervis_subcycle_tom,
+    const double *hypervis_scaling, const double *laplace_scaling, const double *dcmip16_mu,
+    const int *ftype, const int *theta_adv_form, const int *prescribed_wind,
+    const int *use_moisture, const int *disable_diagnostics, const int *use_cpstar,
+    const int *transport_alg, const int *theta_hydrostatic_mode, const char **test_case,
+    const int *dt_remap_factor, const int *dt_tracer_factor, const double *scale_factor,
+    const double *laplacian_rigid_factor, const int *nsplit, const int *pgrad_correction,
+    const double *dp3d_thresh, const double *vtheta_thresh,
+    const int *internal_diagnostics_level, const int *do_3d_turbulence,
+    const double *tom_sponge_start)
+{
+  (void)remap_alg; (void)limiter_option; (void)state_frequency; (void)nu_q; (void)use_moisture;
+  (void)disable_diagnostics; (void)use_cpstar; (void)transport_alg; (void)test_case;
+  (void)dt_remap_factor; (void)dt_tracer_factor; (void)nsplit; (void)internal_diagnostics_level;
+  (void)tom_sponge_start;
+  check_in("hypervis_order", *hypervis_order, {2});
+  check_in("time_step_type", *time_step_type, {1, 4, 5, 7, 9, 10});
+  check_in("theta_advection_form", *theta_adv_form, {0, 1, 2});
+  check_in("theta_hydrostatic_mode", *theta_hydrostatic_mode, {0});   // NH only (north star)
+  check_in("prescribed_wind", *prescribed_wind, {0});
+  check_in("qsize", *qsize, {0});                                     // tracers out of scope
+  check_in("ftype", *ftype, {-1, 0, 2});
+  check_in("do_3d_turbulence", *do_3d_turbulence, {0});
+  if (!(*nu_p > 0) || !(*nu > 0) || !(*nu_div > 0)) fail(3, "nu, nu_p, nu_div must be > 0");
+  if (!(*dp3d_thresh > 0) || !(*vtheta_thresh > 0)) fail(3, "dp3d_thresh, vtheta_thresh must be > 0");
+  if (*hypervis_scaling != 0.0) fail(3, "tensor hyperviscosity (hypervis_scaling != 0) is a next-row item (SURVEY 8f N4)");
+  if (*laplace_scaling != 0.0) fail(3, "laplace_scaling != 0 not supported");
+  if (*dcmip16_mu != 0.0) fail(3, "dcmip16_mu != 0 not supported");
+  if (*rsplit <= 0) fail(3, "rsplit == 0 (vertically Eulerian) not supported by the CUDA path yet");
+  Params &p = S.prm;
+  p.rsplit = *rsplit; p.qsplit = *qsplit; p.tstep_type = *time_step_type;
+  p.theta_advect_form = *theta_adv_form; p.pgrad_correction = *pgrad_correction;
+  p.hypervis_subcycle = *hypervis_subcycle; p.hypervis_subcycle_tom = *hypervis_subcycle_tom;
+  p.hypervis_scaling_on = 0;
+  p.nu = *nu; p.nu_div = *nu_div; p.nu_p = *nu_p; p.nu_s = *nu_s; p.nu_top = *nu_top;
+  p.dp3d_thresh = *dp3d_thresh; p.vtheta_thresh = *vtheta_thresh;
+  p.rearth_inv = *laplacian_rigid_factor;     // == 1/scale_factor on the sphere (namelist_mod.F90:1045-1047)
+  if (fabs(*laplacian_rigid_factor * *scale_factor - 1.0) > 1e-12) fail(3, "planar geometry (laplacian_rigid_factor != 1/scale_factor) not supported");
+  S.hypervis_order = *hypervis_order;
+  S.hypervis_scaling = *hypervis_scaling; S.laplace_scaling = *laplace_scaling;
+  S.params_set = true;
+}
+
+void init_elements_c(const int *nelemd)
+{
+  require(S.nlev > 0, "thetal_b200_set_nlev must precede init_elements_c");
+  const int n = *nelemd;
+  S.prm.nelem = n; S.prm.nlev = S.nlev;
+  S.hD.assign((size_t)n * 64, 0); S.hDinv.assign((size_t)n * 64, 0); S.hmetinv.assign((size_t)n * 64, 0);
+  S.htensorvisc.assign((size_t)n * 64, 0); S.hvec.assign((size_t)n * 96, 0);
+  S.hmetdet.assign((size_t)n * 16, 0); S.hrmetdet.assign((size_t)n * 16, 0); S.hspheremp.assign((size_t)n * 16, 0);
+  S.hrspheremp.assign((size_t)n * 16, 0); S.hfcor.assign((size_t)n * 16, 0); S.hphis.assign((size_t)n * 16, 0);
+  S.hgradphis.assign((size_t)n * 32, 0);
+}
+
+void init_hvcoord_c(const double *ps0, thetal_f90ptr hyam, thetal_f90ptr hyai, thetal_f90ptr hybm, thetal_f90ptr hybi)
+{
+  require(S.nlev > 0, "thetal_b200_set_nlev must precede init_hvcoord_c");
+  const int n = S.nlev;
+  S.hyam.assign(*hyam, *hyam + n); S.hybm.assign(*hybm, *hybm + n);
+  S.hyai.assign(*hyai, *hyai + n + 1); S.hybi.assign(*hybi, *hybi + n + 1);
+  S.prm.ps0 = *ps0; S.prm.ptop = S.hyai[0] * *ps0;
+  S.dp0.resize(n);
+  for (int k = 0; k < n; k++)    // hybvcoord_mod.F90:184-187
+    S.dp0[k] = (S.hyai[k + 1] - S.hyai[k]) * *ps0 + (S.hybi[k + 1] - S.hybi[k]) * *ps0;
+}
+
+void init_time_level_c(const int *nm1, const int *n0, const int *np1, const int *nstep, const int *nstep0)
+{
+  S.nm1 = *nm1 - 1; S.n0 = *n0 - 1; S.np1 = *np1 - 1; S.nstep = *nstep; S.nstep0 = *nstep0;
+}
+
+void init_reference_element_c(thetal_f90ptr deriv, thetal_f90ptr mass)
+{
+  memcpy(S.dvv, *deriv, sizeof S.dvv);
+  memcpy(S.mp, *mass, sizeof S.mp);
+}
+
+void init_elements_2d_c(const int *ie, thetal_f90ptr D, thetal_f90ptr Dinv, thetal_f90ptr fcor,
+    thetal_f90ptr spheremp, thetal_f90ptr rspheremp, thetal_f90ptr metdet, thetal_f90ptr metinv,
+    thetal_f90ptr tensorvisc, thetal_f90ptr vec_sph2cart, const double *sphere_cart_vec,
+    const double *sphere_latlon_vec, thetal_f90ptr tensorvisc2)
+{
+  (void)sphere_cart_vec; (void)sphere_latlon_vec; (void)tensorvisc2;
+  const size_t e = *ie;
+  require((int)e < S.prm.nelem, "init_elements_2d_c: ie out of range");
+  memcpy(&S.hD[e * 64], *D, 64 * sizeof(double));
+  memcpy(&S.hDinv[e * 64], *Dinv, 64 * sizeof(double));
+  memcpy(&S.hmetinv[e * 64], *metinv, 64 * sizeof(double));
+  if (tensorvisc && *tensorvisc) memcpy(&S.htensorvisc[e * 64], *tensorvisc, 64 * sizeof(double));
+  if (vec_sph2cart && *vec_sph2cart) memcpy(&S.hvec[e * 96], *vec_sph2cart, 96 * sizeof(double));
+  memcpy(&S.hfcor[e * 16], *fcor, 16 * sizeof(double));
+  memcpy(&S.hspheremp[e * 16], *spheremp, 16 * sizeof(double));
+  memcpy(&S.hrspheremp[e * 16], *rspheremp, 16 * sizeof(double));
+  memcpy(&S.hmetdet[e * 16], *metdet, 16 * sizeof(double));
+  for (int p = 0; p < 16; p++) S.hrmetdet[e * 16 + p] = 1.0 / S.hmetdet[e * 16 + p];   // cube_mod.F90:274
+}
+
+void init_tensorvisc_c(const int *ie, thetal_f90ptr tensorvisc)
+{
+  memcpy(&S.htensorvisc[(size_t)*ie * 64], *tensorvisc, 64 * sizeof(double));
+}
+void init_tensorvisc2_c(const int *ie, thetal_f90ptr tensorvisc2) { (void)ie; (void)tensorvisc2; }
+
+void init_geopotential_c(const int *ie, thetal_f90ptr phis, thetal_f90ptr gradphis)
+{
+  const size_t e = *ie;
+  memcpy(&S.hphis[e * 16], *phis, 16 * sizeof(double));
+  memcpy(&S.hgradphis[e * 32], *gradphis, 32 * sizeof(double));
+}
+
+void init_diagnostics_c(thetal_f90ptr, thetal_f90ptr, thetal_f90ptr, thetal_f90ptr, thetal_f90ptr,
+                        thetal_f90ptr, thetal_f90ptr) {}
+
+// Create device objects: geometry upload, state/tens allocation (cxx_f90_interface_theta.cpp:568-640)
+void init_functors_c(const int *allocate_buffer)
+{
+  (void)allocate_buffer;
+  if (!S.active) initialize_hommexx_session();
+  if (!S.active) return;
+  require(S.params_set, "init_simulation_params_c must precede init_functors_c");
+  require(!S.hyai.empty(), "init_hvcoord_c must precede init_functors_c");
+  require(!S.hdss.empty(), "finalize_connectivity must precede init_functors_c");
+  if (S.device_ready) return;
+  const int n = S.prm.nelem, nlev = S.nlev;
+  auto up = [&](const std::vector<double> &h) {
+    double *d = dalloc<double>(h.size());
+    CUDA_OK(cudaMemcpy(d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+    return (const double *)d;
+  };
+  S.geo.D = up(S.hD); S.geo.Dinv = up(S.hDinv); S.geo.metinv = up(S.hmetinv);
+  S.geo.tensorvisc = up(S.htensorvisc); S.geo.vec_sph2cart = up(S.hvec);
+  S.geo.metdet = up(S.hmetdet); S.geo.rmetdet = up(S.hrmetdet); S.geo.spheremp = up(S.hspheremp);
+  S.geo.rspheremp = up(S.hrspheremp); S.geo.fcor = up(S.hfcor); S.geo.phis = up(S.hphis);
+  S.geo.gradphis = up(S.hgradphis);
+  int *dd = dalloc<int>(S.hdss.size());
+  CUDA_OK(cudaMemcpy(dd, S.hdss.data(), S.hdss.size() * sizeof(int), cudaMemcpyHostToDevice));
+  S.geo.dss_src = dd;
+  for (int t = 0; t < NTL; t++) S.tl[t] = alloc_state(n, nlev);
+  S.tensA = alloc_state(n, nlev);
+  S.tensB = alloc_state(n, nlev);
+  S.der.vn0 = dalloc<double>((size_t)n * 32 * nlev);
+  S.der.eta_dot_dpdn = dalloc<double>((size_t)n * 16 * (nlev + 1));
+  S.der.omega_p = dalloc<double>((size_t)n * 16 * nlev);
+  S.ref.theta_ref = dalloc<double>((size_t)n * 16 * nlev);
+  S.ref.dp_ref = dalloc<double>((size_t)n * 16 * nlev);
+  S.ref.phi_ref = dalloc<double>((size_t)n * 16 * (nlev + 1));
+  S.d_err = dalloc<int>(1); S.d_maxiter = dalloc<int>(1); S.d_maxdelta = dalloc<unsigned long long>(1);
+  if (S.nu_scale_top.empty()) S.nu_scale_top.assign(nlev, 0.0);
+  upload_constants(S.dvv, S.mp, S.hybi.data(), S.dp0.data(), S.nu_scale_top.data(), nlev);
+  CUDA_OK(cudaDeviceSynchronize());
+  S.device_ready = true;
+}
+
+void init_boundary_exchanges_c(void) {}
+void initialize_dp3d_from_ps_c(void) { fail(3, "initialize_dp3d_from_ps_c: pass dp3d through init_elements_states_c"); }
+
+}  // extern "C"
+
+namespace {
+
+void copy_state_h2d(const double *h, double *const d[NTL], size_t per_elem)
+{ // h: [ie][tl][per_elem]  ->  d[tl]: [ie][per_elem]
+  const int n = S.prm.nelem;
+  for (int t = 0; t < NTL; t++)
+    CUDA_OK(cudaMemcpy2DAsync(d[t], per_elem * sizeof(double), h + t * per_elem, NTL * per_elem * sizeof(double),
+                              per_elem * sizeof(double), n, cudaMemcpyHostToDevice, S.stream));
+}
+void copy_state_d2h(double *h, double *const d[NTL], size_t per_elem)
+{
+  const int n = S.prm.nelem;
+  for (int t = 0; t < NTL; t++)
+    CUDA_OK(cudaMemcpy2DAsync(h + t * per_elem, NTL * per_elem * sizeof(double), d[t], per_elem * sizeof(double),
+                              per_elem * sizeof(double), n, cudaMemcpyDeviceToHost, S.stream));
+}
+
+void check_device_errors(const char *where)
+{
+  int err = 0;
+  CUDA_OK(cudaMemcpyAsync(&err, S.d_err, sizeof(int), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  if (err & ERR_EOS_BAD_STATE) {     // eos.F90:128-145 aborts the job
+    CUDA_OK(cudaMemsetAsync(S.d_err, 0, sizeof(int), S.stream));
+    fail(10, std::string("EOS bad state: d(phi), dp3d or vtheta_dp < 0 (detected in ") + where + ")");
+  }
+  if (err & ERR_DIRK_NOT_CONVERGED) {  // imex_mod.F90:353-357: warning only
+    fprintf(stderr, "thetal_b200: WARNING: IMEX solver failed b/c max iteration count was met\n");
+    CUDA_OK(cudaMemsetAsync(S.d_err, 0, sizeof(int), S.stream));
+  }
+}
+
+// ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
+void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3)
+{
+  CaarArgs a;
+  a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
+  a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
+  launch_caar_pre(a, S.stream);
+  DssArgs d;
+  d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
+  d.do_limiter = (s3 != 0.0);
+  launch_caar_dss_post(d, S.stream);
+  S.launches += 2;
+}
+
+void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
+{
+  DirkArgs a;
+  a.np1 = S.tl[np1]; a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.geo = S.geo; a.prm = S.prm;
+  a.dt2 = dt2; a.alphadt_n0 = a_n0; a.alphadt_nm1 = a_nm1;
+  a.err = S.d_err; a.max_iter = S.d_maxiter; a.max_deltaerr_bits = S.d_maxdelta;
+  launch_dirk(a, S.stream);
+  S.launches += 1;
+}
+
+void run_hypervis(int nt, double dt2, double eta_ave_w)
+{
+  (void)eta_ave_w;   // dpdiss_ave / dpdiss_biharmonic diagnostics (PA:651-656) are not carried
+  HvArgs a;
+  a.st = S.tl[nt]; a.geo = S.geo; a.ref = S.ref; a.prm = S.prm;
+  const int hvs = S.prm.hypervis_subcycle;
+  // viscosity_theta.F90:77-83: nu_ratio1 = nu_div/nu on the first laplacian, nu_ratio2 = 1
+  const double nu_ratio1 = (S.prm.nu_div != S.prm.nu) ? S.prm.nu_div / S.prm.nu : 1.0;
+  for (int ic = 0; ic < hvs; ic++) {
+    a.dt = dt2 / hvs;
+    a.th_is_theta = ic > 0; a.last_subcycle = (ic == hvs - 1);
+    a.nu_ratio = nu_ratio1; a.tin = S.tensB; a.tout = S.tensA; launch_hv(0, a, S.stream);
+    a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB; launch_hv(1, a, S.stream);
+    a.tin = S.tensB; a.tout = S.tensA; launch_hv(2, a, S.stream);
+    S.launches += 3;
+  }
+  if (hvs == 0) fail(3, "hypervis_subcycle must be >= 1");
+  if (S.prm.nu_top > 0 && S.prm.hypervis_subcycle_tom > 0 && S.prm.nlev_tom > 0) {   // PA:780
+    const int nt_ = S.prm.hypervis_subcycle_tom;
+    for (int ic = 0; ic < nt_; ic++) {
+      a.dt = dt2 / nt_; a.th_is_theta = 0; a.last_subcycle = 0;
+      a.tin = S.tensB; a.tout = S.tensA; launch_hv(3, a, S.stream);
+      a.tin = S.tensA; a.tout = S.tensB; launch_hv(4, a, S.stream);
+      S.launches += 2;
+    }
+  }
+}
+
+void run_combo(int kind, int ia, int ib, int ic)
+{
+  ComboArgs c;
+  c.a = S.tl[ia]; c.b = S.tl[ib]; c.c = S.tl[ic]; c.geo = S.geo; c.prm = S.prm; c.kind = kind;
+  launch_combo(c, S.stream);
+  S.launches += 1;
+}
+
+// PA:81-513
+void run_prim_advance_exp(double dt, int nm1, int n0, int np1)
+{
+  const double eta_ave_w = 1.0 / S.prm.qsplit;                                       // PA:137
+  launch_wbc(S.tl[n0], S.geo, S.prm.nelem, S.prm.nlev, S.stream);                    // PA:140-143
+  S.launches += 1;
+  switch (S.prm.tstep_type) {
+    case 1:
+      run_caar(np1, n0, n0, dt / 2, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, dt, eta_ave_w, 1, 1, 1);
+      break;
+    case 4:
+      run_caar(np1, n0, n0, dt / 4, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, dt / 6, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, 3 * dt / 8, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, dt / 2, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 1, 1);
+      break;
+    case 5:
+      run_caar(nm1, n0, n0, dt / 5, eta_ave_w / 4, 1, 1, 1);
+      run_caar(np1, n0, nm1, dt / 5, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, dt / 3, 0.0, 1, 1, 1);
+      run_caar(np1, n0, np1, 2 * dt / 3, 0.0, 1, 1, 1);
+      run_combo(5, nm1, n0, n0);
+      run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 1, 1);
+      break;
+    case 7: {
+      const double a1 = 0.0, a2 = 1 - a1;
+      double dt2 = dt / 4;
+      run_caar(np1, n0, n0, dt2, 0.0, 1, 0, 1);  run_dirk(nm1, 0.0, n0, a1 * dt2, np1, a2 * dt2);
+      dt2 = dt / 6;
+      run_caar(nm1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt2, nm1, a2 * dt2);
+      dt2 = 3 * dt / 8;
+      run_caar(np1, n0, nm1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt2, np1, a2 * dt2);
+      dt2 = dt / 2;
+      run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt2, np1, a2 * dt2);
+      run_caar(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt, np1, a2 * dt);
+      break;
+    }
+    case 9: {
+      run_caar(nm1, n0, n0, dt / 5, eta_ave_w / 4, 1, 0, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt / 5);
+      run_caar(np1, n0, nm1, dt / 5, 0.0, 1, 0, 1);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 5);
+      run_caar(np1, n0, np1, dt / 3, 0.0, 1, 0, 1);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 3);
+      run_caar(np1, n0, np1, 2 * dt / 3, 0.0, 1, 0, 1);       run_dirk(nm1, 0.0, n0, 0.0, np1, 2 * dt / 3);
+      run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1);
+      run_combo(9, np1, nm1, n0);
+      const double a1 = 5 * dt / 18, a2 = dt / 36, a3 = 8 * dt / 18;
+      run_dirk(nm1, a2, n0, a1, np1, a3);
+      break;
+    }
+    case 10: {
+      double dt2 = dt / 4;
+      run_caar(nm1, n0, n0, dt2, 0.0, 1, 0, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt2);
+      dt2 = dt / 6;
+      run_caar(np1, n0, nm1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      dt2 = 3 * dt / 8;
+      run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      dt2 = dt / 2;
+      run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      run_caar(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 0, 1);
+      const double a1 = .24362, a2 = .34184, a3 = 1 - (a1 + a2);
+      run_dirk(nm1, a2 * dt, n0, a1 * dt, np1, a3 * dt);
+      break;
+    }
+    default: fail(3, "bad choice of tstep_type");
+  }
+  if (S.hypervis_order == 2 && S.prm.nu > 0) run_hypervis(np1, dt, eta_ave_w);          // PA:499-500
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------- state transfer
+void init_elements_states_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vtheta_dp,
+    thetal_f90ptr phinh_i, thetal_f90ptr dp3d, thetal_f90ptr qdp, thetal_f90ptr ps_v)
+{
+  (void)qdp; (void)ps_v;
+  require(S.device_ready, "init_functors_c must precede init_elements_states_c");
+  if (!S.device_ready) return;
+  const size_t nlev = S.nlev;
+  double *dv[NTL], *dw[NTL], *dth[NTL], *dphi[NTL], *ddp[NTL];
+  for (int t = 0; t < NTL; t++) { dv[t] = S.tl[t].v; dw[t] = S.tl[t].w; dth[t] = S.tl[t].th; dphi[t] = S.tl[t].phi; ddp[t] = S.tl[t].dp; }
+  copy_state_h2d(*v, dv, 32 * nlev);
+  copy_state_h2d(*w_i, dw, 16 * (nlev + 1));
+  copy_state_h2d(*vtheta_dp, dth, 16 * nlev);
+  copy_state_h2d(*phinh_i, dphi, 16 * (nlev + 1));
+  copy_state_h2d(*dp3d, ddp, 16 * nlev);
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+}
+
+void cxx_push_results_to_f90(thetal_f90ptr_out v, thetal_f90ptr_out w_i, thetal_f90ptr_out vtheta_dp,
+    thetal_f90ptr_out phinh_i, thetal_f90ptr_out dp3d, thetal_f90ptr_out ps_v, thetal_f90ptr_out qdp,
+    thetal_f90ptr_out q, thetal_f90ptr_out omega_p)
+{
+  (void)ps_v; (void)qdp; (void)q;
+  require(S.device_ready, "no device state");
+  if (!S.device_ready) return;
+  const size_t nlev = S.nlev;
+  double *dv[NTL], *dw[NTL], *dth[NTL], *dphi[NTL], *ddp[NTL];
+  for (int t = 0; t < NTL; t++) { dv[t] = S.tl[t].v; dw[t] = S.tl[t].w; dth[t] = S.tl[t].th; dphi[t] = S.tl[t].phi; ddp[t] = S.tl[t].dp; }
+  copy_state_d2h(*v, dv, 32 * nlev);
+  copy_state_d2h(*w_i, dw, 16 * (nlev + 1));
+  copy_state_d2h(*vtheta_dp, dth, 16 * nlev);
+  copy_state_d2h(*phinh_i, dphi, 16 * (nlev + 1));
+  copy_state_d2h(*dp3d, ddp, 16 * nlev);
+  if (omega_p && *omega_p)
+    CUDA_OK(cudaMemcpyAsync(*omega_p, S.der.omega_p, (size_t)S.prm.nelem * 16 * nlev * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  check_device_errors("cxx_push_results_to_f90");
+}
+
+void push_test_state_to_c(thetal_f90ptr ps_v, thetal_f90ptr dp3d, thetal_f90ptr vtheta_dp,
+    thetal_f90ptr phinh_i, thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr eta_dot_dpdn, thetal_f90ptr vn0)
+{
+  (void)eta_dot_dpdn; (void)vn0;
+  init_elements_states_c(v, w_i, vtheta_dp, phinh_i, dp3d, nullptr, ps_v);
+}
+
+void init_reference_states_c(thetal_f90ptr theta_ref, thetal_f90ptr dp_ref, thetal_f90ptr phi_ref,
+                             thetal_f90ptr nu_scale_top)
+{
+  require(S.device_ready, "init_functors_c must precede init_reference_states_c");
+  if (!S.device_ready) return;
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  CUDA_OK(cudaMemcpy((void *)S.ref.theta_ref, *theta_ref, n * 16 * nlev * sizeof(double), cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy((void *)S.ref.dp_ref, *dp_ref, n * 16 * nlev * sizeof(double), cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy((void *)S.ref.phi_ref, *phi_ref, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyHostToDevice));
+  S.nu_scale_top.assign(*nu_scale_top, *nu_scale_top + nlev);
+  int ntom = 0;                                     // model_init_mod.F90:128
+  for (size_t k = 0; k < nlev; k++) if (S.nu_scale_top[k] > 0) ntom = (int)k + 1;
+  S.prm.nlev_tom = ntom;
+  upload_constants(nullptr, nullptr, nullptr, nullptr, S.nu_scale_top.data(), (int)nlev);
+}
+
+void push_forcing_to_c(const double *, const double *, const double *, const double *, const double *)
+{
+  fail(3, "push_forcing_to_c: physics forcing (applyCAMforcing) is outside the hot path of this build");
+}
+
+void sync_diagnostics_to_host_c(void)
+{
+  if (!S.device_ready) return;
+  unsigned long long bits = 0; int it = 0;
+  CUDA_OK(cudaMemcpyAsync(&bits, S.d_maxdelta, sizeof bits, cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaMemcpyAsync(&it, S.d_maxiter, sizeof it, cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  S.max_itercnt = it;
+  memcpy(&S.max_deltaerr, &bits, sizeof bits);
+}
+
+void thetal_b200_get_derived(double *vn0, double *eta_dot_dpdn, double *omega_p)
+{
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  if (vn0) CUDA_OK(cudaMemcpy(vn0, S.der.vn0, n * 32 * nlev * sizeof(double), cudaMemcpyDeviceToHost));
+  if (eta_dot_dpdn) CUDA_OK(cudaMemcpy(eta_dot_dpdn, S.der.eta_dot_dpdn, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyDeviceToHost));
+  if (omega_p) CUDA_OK(cudaMemcpy(omega_p, S.der.omega_p, n * 16 * nlev * sizeof(double), cudaMemcpyDeviceToHost));
+}
+void thetal_b200_zero_derived(void)
+{
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  CUDA_OK(cudaMemsetAsync(S.der.vn0, 0, n * 32 * nlev * sizeof(double), S.stream));
+  CUDA_OK(cudaMemsetAsync(S.der.eta_dot_dpdn, 0, n * 16 * (nlev + 1) * sizeof(double), S.stream));
+  CUDA_OK(cudaMemsetAsync(S.der.omega_p, 0, n * 16 * nlev * sizeof(double), S.stream));
+}
+void thetal_b200_sync(void)
+{
+  if (!S.device_ready) return;
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  CUDA_OK(cudaGetLastError());
+  check_device_errors("thetal_b200_sync");
+}
+long thetal_b200_launch_count(void) { return S.launches; }
+
+// ---------------------------------------------------------------- the step
+static bool tl_ok(int t) { return t >= 0 && t < NTL; }
+
+void caar_c(const int *np1, const int *nm1, const int *n0, const double *dt2, const double *eta_ave_w,
+            const double *scale1, const double *scale2, const double *scale3)
+{
+  require(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "caar_c: bad state/time level");
+  run_caar(*np1, *nm1, *n0, *dt2, *eta_ave_w, *scale1, *scale2, *scale3);
+  thetal_b200_sync();
+}
+
+void dirk_c(const int *nm1, const double *alphadt_nm1, const int *n0, const double *alphadt_n0,
+            const int *np1, const double *dt2, int *itercount, double *itererr)
+{
+  require(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "dirk_c: bad state/time level");
+  CUDA_OK(cudaMemsetAsync(S.d_maxiter, 0, sizeof(int), S.stream));
+  CUDA_OK(cudaMemsetAsync(S.d_maxdelta, 0, sizeof(unsigned long long), S.stream));
+  run_dirk(*nm1, *alphadt_nm1, *n0, *alphadt_n0, *np1, *dt2);
+  thetal_b200_sync();
+  sync_diagnostics_to_host_c();
+  if (itercount) *itercount = S.max_itercnt;
+  if (itererr) *itererr = S.max_deltaerr;
+}
+
+void advance_hypervis_c(const int *nt, const double *dt2, const double *eta_ave_w)
+{
+  require(S.device_ready && tl_ok(*nt), "advance_hypervis_c: bad state/time level");
+  run_hypervis(*nt, *dt2, *eta_ave_w);
+  thetal_b200_sync();
+}
+
+void prim_advance_exp_c(const double *dt, const int *nm1, const int *n0, const int *np1,
+                        const int *nstep, const int *compute_diagnostics)
+{
+  (void)nstep; (void)compute_diagnostics;
+  require(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "prim_advance_exp_c: bad state/time level");
+  run_prim_advance_exp(*dt, *nm1, *n0, *np1);
+  thetal_b200_sync();
+}
+
+// prim_run_subcycle (prim_driver_base.F90:1024-1195, prim_driver.cpp:60-181) restricted to the
+// dynamics: qsize=0, no forcing, and NO vertical remap -- each call advances
+// `rsplit` dynamics steps of length tstep and rotates the time levels (time_mod.F90:109-138).
+void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int *np1,
+                         const int *next_output_step, const int *nsplit_iter)
+{
+  (void)next_output_step; (void)nsplit_iter;
+  require(S.device_ready, "prim_run_subcycle_c before init");
+  int t_nm1 = *nm1 - 1, t_n0 = *n0 - 1, t_np1 = *np1 - 1;    // Fortran passes 1-based levels
+  require(tl_ok(t_nm1) && tl_ok(t_n0) && tl_ok(t_np1), "prim_run_subcycle_c: bad time level");
+  const int nsub = S.prm.rsplit > 0 ? S.prm.rsplit : 1;
+  for (int r = 0; r < nsub; r++) {
+    run_prim_advance_exp(*tstep, t_nm1, t_n0, t_np1);
+    const int tmp = t_np1; t_np1 = t_nm1; t_nm1 = t_n0; t_n0 = tmp;                  // leapfrog update
+    (*nstep)++;
+  }
+  thetal_b200_sync();
+  *nm1 = t_nm1 + 1; *n0 = t_n0 + 1; *np1 = t_np1 + 1;
+  S.nm1 = t_nm1; S.n0 = t_n0; S.np1 = t_np1; S.nstep = *nstep;
+}
+
+double thetal_b200_time_steps(const double *dt, const int *nsteps, int *nm1, int *n0, int *np1)
+{
+  require(S.device_ready, "thetal_b200_time_steps before init");
+  int t_nm1 = *nm1, t_n0 = *n0, t_np1 = *np1;
+  CUDA_OK(cudaEventRecord(S.ev0, S.stream));
+  for (int s = 0; s < *nsteps; s++) {
+    run_prim_advance_exp(*dt, t_nm1, t_n0, t_np1);
+    const int tmp = t_np1; t_np1 = t_nm1; t_nm1 = t_n0; t_n0 = tmp;
+  }
+  CUDA_OK(cudaEventRecord(S.ev1, S.stream));
+  CUDA_OK(cudaEventSynchronize(S.ev1));
+  float ms = 0;
+  CUDA_OK(cudaEventElapsedTime(&ms, S.ev0, S.ev1));
+  *nm1 = t_nm1; *n0 = t_n0; *np1 = t_np1;
+  check_device_errors("thetal_b200_time_steps");
+  return (double)ms;
+}
+
+}  // extern "C"

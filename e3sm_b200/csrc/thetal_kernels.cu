@@ -1,0 +1,1060 @@
+// Hand-written sm_100a FP64 kernels for HOMME's theta-l nonhydrostatic dycore step.
+// Reference arithmetic (H/ = components/homme/ in the reference tree):
+//   PA  = H/src/theta-l/share/prim_advance_mod.F90   (compute_andor_apply_rhs :1023-1819,
+//                                                      advance_hypervis :546-862, limiter :1822-1931)
+//   DM  = H/src/share/derivative_mod.F90              (sphere operators)
+//   IM  = H/src/theta-l/share/imex_mod.F90            (compute_stage_value_dirk :60-364)
+//   EOS = H/src/theta-l/share/eos.F90
+//   VT  = H/src/theta-l/share/viscosity_theta.F90
+// Design: one CTA per element; a half-warp owns the 16 GLL points of one level, so every 4x4
+// derivative contraction is 8 shared-memory reads + 8 FMAs held in registers (far too small for
+// tensor cores).  Element columns are staged through shared memory once; DSS is a pull-style
+// gather from the neighbours' pre-DSS ("tens") values, so there are no edge buffers.
+#include "thetal_kernels.h"
+#include <cstdio>
+
+namespace thetal {
+
+constexpr int MAXLEV = 128;
+__constant__ double c_dvv[16];            // c_dvv[l*4+i] = Dvv(i,l)
+__constant__ double c_mp[16];
+__constant__ double c_hybi[MAXLEV + 1];
+__constant__ double c_dp0[MAXLEV];
+__constant__ double c_nu_scale_top[MAXLEV];
+
+void upload_constants(const double *dvv, const double *mp, const double *hybi, const double *dp0,
+                      const double *nu_scale_top, int nlev)
+{
+  if (dvv) cudaMemcpyToSymbol(c_dvv, dvv, 16 * sizeof(double));
+  if (mp) cudaMemcpyToSymbol(c_mp, mp, 16 * sizeof(double));
+  if (hybi) cudaMemcpyToSymbol(c_hybi, hybi, (nlev + 1) * sizeof(double));
+  if (dp0) cudaMemcpyToSymbol(c_dp0, dp0, nlev * sizeof(double));
+  if (nu_scale_top) cudaMemcpyToSymbol(c_nu_scale_top, nu_scale_top, nlev * sizeof(double));
+}
+
+// ------------------------------------------------------------------------------------------
+// Per-thread view of one GLL point (a,b) = (i,j) of an element: derivative rows + metric terms.
+// ------------------------------------------------------------------------------------------
+struct Pt {
+  int p, a, b;
+  double da[4], db[4];          // Dvv(i,a), Dvv(i,b)
+  double Dinv[4], D[4];         // index b2*2+a2 of X(i,j,a2,b2)
+  double metdet, rmetdet_sfi, sfi;
+};
+
+__device__ __forceinline__ void pt_init(Pt &t, const Geo &g, int ie, int p, double sfi)
+{
+  t.p = p; t.a = p & 3; t.b = p >> 2;
+#pragma unroll
+  for (int i = 0; i < 4; i++) { t.da[i] = c_dvv[t.a * 4 + i]; t.db[i] = c_dvv[t.b * 4 + i]; }
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    t.Dinv[q] = g.Dinv[(size_t)ie * 64 + q * 16 + p];
+    t.D[q] = g.D[(size_t)ie * 64 + q * 16 + p];
+  }
+  t.metdet = g.metdet[(size_t)ie * 16 + p];
+  t.rmetdet_sfi = g.rmetdet[(size_t)ie * 16 + p] * sfi;
+  t.sfi = sfi;
+}
+
+// x-derivative  v1(a,b) = sum_i Dvv(i,a) s(i,b)  and y-derivative v2(a,b) = sum_i Dvv(i,b) s(a,i)
+// of a 16-point tile s[] (i fastest) in shared memory.
+__device__ __forceinline__ double ddx(const Pt &t, const double *s)
+{
+  const double *r = s + t.b * 4;
+  double acc = t.da[0] * r[0];
+  acc = fma(t.da[1], r[1], acc); acc = fma(t.da[2], r[2], acc); acc = fma(t.da[3], r[3], acc);
+  return acc;
+}
+__device__ __forceinline__ double ddy(const Pt &t, const double *s)
+{
+  const double *c = s + t.a;
+  double acc = t.db[0] * c[0];
+  acc = fma(t.db[1], c[4], acc); acc = fma(t.db[2], c[8], acc); acc = fma(t.db[3], c[12], acc);
+  return acc;
+}
+// DM:410-450
+__device__ __forceinline__ void gradient_sphere(const Pt &t, const double *s, double &g1, double &g2)
+{
+  const double v1 = ddx(t, s) * t.sfi, v2 = ddy(t, s) * t.sfi;
+  g1 = t.Dinv[0] * v1 + t.Dinv[1] * v2;
+  g2 = t.Dinv[2] * v1 + t.Dinv[3] * v2;
+}
+// DM:1021-1068, first half: contravariant, metdet-weighted components to be written to a tile
+__device__ __forceinline__ void div_prep(const Pt &t, double v1, double v2, double &gv1, double &gv2)
+{
+  gv1 = t.metdet * (t.Dinv[0] * v1 + t.Dinv[2] * v2);
+  gv2 = t.metdet * (t.Dinv[1] * v1 + t.Dinv[3] * v2);
+}
+__device__ __forceinline__ double div_finish(const Pt &t, const double *sgv1, const double *sgv2)
+{
+  return (ddx(t, sgv1) + ddy(t, sgv2)) * t.rmetdet_sfi;
+}
+// DM:915-966
+__device__ __forceinline__ void vort_prep(const Pt &t, double v1, double v2, double &vco1, double &vco2)
+{
+  vco1 = t.D[0] * v1 + t.D[1] * v2;
+  vco2 = t.D[2] * v1 + t.D[3] * v2;
+}
+__device__ __forceinline__ double vort_finish(const Pt &t, const double *svco1, const double *svco2)
+{
+  return (ddx(t, svco2) - ddy(t, svco1)) * t.rmetdet_sfi;
+}
+
+// EOS:175-183  pnh = p0*(p_over_exner/p0)^(1/(1-kappa))
+__device__ __forceinline__ double eos_pnh(double p_over_exner)
+{
+  return P0 * pow(p_over_exner / P0, 1.0 / (1.0 - KAPPA));
+}
+
+// ==========================================================================================
+// compute_andor_apply_rhs, element-local part before the exchange (PA:1113-1702), NH, rsplit>0.
+// Writes the mass-weighted, not yet DSS'd new state into `tens`.
+// ==========================================================================================
+
+constexpr int CAAR_THREADS = 256;
+constexpr int CAAR_SLOTS = 10;    // scratch tiles per half-warp
+
+__host__ __device__ inline size_t caar_smem_bytes(int nlev)
+{
+  const size_t nlevp = nlev + 1;
+  // v(2) dp th pnh exn div : 7*nlev tiles ; w phi : 2*nlevp tiles ; scratch
+  return sizeof(double) * 16 * (7 * (size_t)nlev + 2 * nlevp + (CAAR_THREADS / 16) * CAAR_SLOTS);
+}
+
+__global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArgs A)
+{
+  extern __shared__ double smem[];
+  const int nlev = A.prm.nlev, nlevp = nlev + 1;
+  const int ie = blockIdx.x, tid = threadIdx.x;
+  double *sv = smem;                       // [k][2][16]
+  double *sdp = sv + 32 * nlev;            // [k][16]
+  double *sth = sdp + 16 * nlev;
+  double *sw = sth + 16 * nlev;            // [nlevp][16]
+  double *sphi = sw + 16 * nlevp;
+  double *spnh = sphi + 16 * nlevp;        // [k][16]
+  double *sexn = spnh + 16 * nlev;
+  double *sdiv = sexn + 16 * nlev;
+  double *scr = sdiv + 16 * nlev + (tid >> 4) * (CAAR_SLOTS * 16);   // this half-warp's tiles
+
+  // ---- phase 0: stage the n0 columns of this element (contiguous per field) ----
+  {
+    const double *gv = A.n0.v + (size_t)ie * 32 * nlev, *gdp = A.n0.dp + (size_t)ie * 16 * nlev;
+    const double *gth = A.n0.th + (size_t)ie * 16 * nlev;
+    const double *gw = A.n0.w + (size_t)ie * 16 * nlevp, *gphi = A.n0.phi + (size_t)ie * 16 * nlevp;
+    for (int q = tid; q < 32 * nlev; q += CAAR_THREADS) sv[q] = gv[q];
+    for (int q = tid; q < 16 * nlev; q += CAAR_THREADS) { sdp[q] = gdp[q]; sth[q] = gth[q]; }
+    for (int q = tid; q < 16 * nlevp; q += CAAR_THREADS) { sw[q] = gw[q]; sphi[q] = gphi[q]; }
+  }
+  __syncthreads();
+  // ---- phase 1: EOS (EOS:175-183), one pow per point-level ----
+  {
+    int bad = 0;
+    for (int q = tid; q < 16 * nlev; q += CAAR_THREADS) {
+      const double dphi = sphi[q + 16] - sphi[q];
+      const double th = sth[q], dp = sdp[q];
+      if (th < 0 || dp < 0 || dphi > 0) bad = 1;
+      const double poe = RGAS * th / (-dphi);
+      const double pnh = eos_pnh(poe);
+      spnh[q] = pnh;
+      sexn[q] = pnh / poe;
+    }
+    if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
+  }
+  __syncthreads();
+
+  // ---- phase 2: tendencies, a half-warp per level ----
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = CAAR_THREADS / 16;
+  Pt t;
+  pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
+  const double fcor = A.geo.fcor[(size_t)ie * 16 + p], spheremp = A.geo.spheremp[(size_t)ie * 16 + p];
+  const double gps1 = A.geo.gradphis[(size_t)ie * 32 + p], gps2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
+  const double s1 = A.scale1, s2 = A.scale2, s3 = A.scale3, dt2 = A.dt2;
+  const bool accum = (A.eta_ave_w != 0.0);
+  const int niter = (nlev + KS - 1) / KS;
+
+  for (int it = 0; it < niter; it++) {
+    const int kk = it * KS + kslot;
+    const bool act = kk < nlev;
+    const int k = act ? kk : nlev - 1;     // inactive half-warps redo the last level, never store
+    const int q = k * 16 + p;
+    const double dp = sdp[q], th = sth[q], v1 = sv[k * 32 + p], v2 = sv[k * 32 + 16 + p];
+    const double wk = sw[q], wk1 = sw[q + 16];
+    const double pnh = spnh[q], exner = sexn[q];
+    const double theta = th / dp;                                                  // PA:1116
+    // interface quantities at k (top of the layer) and k+1 (bottom)
+    double dpi_k, v1i_k, v2i_k, mu_k;                                               // PA:1156-1170, EOS:198-208
+    if (k == 0) {
+      dpi_k = dp; v1i_k = v1; v2i_k = v2;
+      mu_k = 2 * (pnh - A.prm.ptop) / dpi_k;
+    } else {
+      const double dpm = sdp[q - 16];
+      dpi_k = (dp + dpm) / 2;
+      v1i_k = (dp * v1 + dpm * sv[(k - 1) * 32 + p]) / (2 * dpi_k);
+      v2i_k = (dp * v2 + dpm * sv[(k - 1) * 32 + 16 + p]) / (2 * dpi_k);
+      mu_k = (pnh - spnh[q - 16]) / dpi_k;
+    }
+    double mu_k1;
+    if (k == nlev - 1) mu_k1 = 2 * ((pnh + dp / 2) - pnh) / dp;                      // EOS:193,205
+    else mu_k1 = (spnh[q + 16] - pnh) / ((sdp[q + 16] + dp) / 2);
+
+    // tiles for the operators that act on computed quantities
+    double gv1, gv2, vc1, vc2, gt1, gt2;
+    div_prep(t, v1 * dp, v2 * dp, gv1, gv2);                                        // PA:1188-1192
+    vort_prep(t, v1, v2, vc1, vc2);
+    scr[0 * 16 + p] = gv1; scr[1 * 16 + p] = gv2; scr[2 * 16 + p] = vc1; scr[3 * 16 + p] = vc2;
+    if (A.prm.theta_advect_form != 1) {
+      div_prep(t, v1 * th, v2 * th, gt1, gt2);                                      // PA:1373-1375
+      scr[4 * 16 + p] = gt1; scr[5 * 16 + p] = gt2;
+    }
+    scr[6 * 16 + p] = (wk * wk + wk1 * wk1) / 4;                                    // PA:1401
+    scr[7 * 16 + p] = (v1 * v1 + v2 * v2) / 2;                                      // PA:1409
+    if (A.prm.theta_advect_form != 0) { scr[8 * 16 + p] = theta; scr[9 * 16 + p] = theta * exner; }
+    __syncwarp();
+
+    const double divdp = div_finish(t, scr, scr + 16);
+    const double vort = vort_finish(t, scr + 32, scr + 48);
+    double gphi1_k, gphi2_k, gphi1_k1, gphi2_k1, gw1_k, gw2_k, gw1_k1, gw2_k1;
+    gradient_sphere(t, sphi + k * 16, gphi1_k, gphi2_k);                            // PA:1323
+    gradient_sphere(t, sphi + (k + 1) * 16, gphi1_k1, gphi2_k1);
+    gradient_sphere(t, sw + k * 16, gw1_k, gw2_k);                                  // PA:1325
+    gradient_sphere(t, sw + (k + 1) * 16, gw1_k1, gw2_k1);
+    double wv1, wv2, ke1, ke2, ge1, ge2;
+    gradient_sphere(t, scr + 6 * 16, wv1, wv2);                                     // PA:1403
+    gradient_sphere(t, scr + 7 * 16, ke1, ke2);                                     // PA:1410
+    gradient_sphere(t, sexn + k * 16, ge1, ge2);                                    // PA:1411
+
+    // theta tendency PA:1372-1398
+    double div_v_theta;
+    if (A.prm.theta_advect_form == 0) {
+      div_v_theta = div_finish(t, scr + 64, scr + 80);
+    } else {
+      double gth1, gth2;
+      gradient_sphere(t, scr + 8 * 16, gth1, gth2);
+      const double nc = theta * divdp + dp * v1 * gth1 + dp * v2 * gth2;
+      if (A.prm.theta_advect_form == 1) div_v_theta = nc;
+      else div_v_theta = div_finish(t, scr + 64, scr + 80) / 2 + nc / 2;
+    }
+    const double theta_tens = (-div_v_theta) * s1;                                  // theta_vadv = 0 (rsplit>0)
+
+    // w, phi tendencies at interface k  PA:1326-1344
+    const double v_gradw = v1i_k * gw1_k + v2i_k * gw2_k;
+    const double w_tens = (-v_gradw) * s1 - s2 * G_GRAV * (1 - mu_k);
+    const double v_gradphi = v1i_k * gphi1_k + v2i_k * gphi2_k;
+    double phi_tens = (-v_gradphi) * s1 + s2 * G_GRAV * wk;
+    if (s1 != s2) phi_tens = phi_tens + (s1 - s2) * (v1i_k * gps1 + v2i_k * gps2) * c_hybi[k];
+
+    // momentum PA:1404-1509
+    wv1 = wv1 - (wk * gw1_k + wk1 * gw1_k1) / 2;
+    wv2 = wv2 - (wk * gw2_k + wk1 * gw2_k1) / 2;
+    double gp1 = CP * theta * ge1, gp2 = CP * theta * ge2;
+    if (A.prm.theta_advect_form == 2) {                                             // PA:1446-1452
+      double gte1, gte2, gth1, gth2;
+      gradient_sphere(t, scr + 9 * 16, gte1, gte2);
+      gradient_sphere(t, scr + 8 * 16, gth1, gth2);
+      gp1 = (gp1 + CP * (gte1 - exner * gth1)) / 2;
+      gp2 = (gp2 + CP * (gte2 - exner * gth2)) / 2;
+    }
+    double mg1 = (mu_k * gphi1_k + mu_k1 * gphi1_k1) / 2;                           // PA:1455-1458
+    double mg2 = (mu_k * gphi2_k + mu_k1 * gphi2_k1) / 2;
+    if (A.prm.pgrad_correction == 1) {                                              // PA:1460-1477
+      __syncwarp();
+      scr[0 * 16 + p] = log(exner);
+      __syncwarp();
+      double gl1, gl2;
+      gradient_sphere(t, scr, gl1, gl2);
+      const double T0 = TREF - TREF_LAPSE * TREF * CP / G_GRAV;
+      mg1 = mg1 + CP * T0 * (gl1 - ge1 / exner);
+      mg2 = mg2 + CP * T0 * (gl2 - ge2 / exner);
+    }
+    const double vt1 = (v2 * (fcor + vort) - ke1 - mg1 - gp1 - wv1) * s1;           // PA:1495-1506 (v_vadv = 0)
+    const double vt2 = (-v1 * (fcor + vort) - ke2 - mg2 - gp2 - wv2) * s1;
+
+    if (act) {
+      // PA:1674-1690  X(np1) = spheremp*(scale3*X(nm1) + dt2*tens); reads of nm1 straight from HBM
+      const size_t gq = (size_t)ie * 16 * nlev + q, gqv = (size_t)ie * 32 * nlev + k * 32 + p;
+      const size_t gqi = (size_t)ie * 16 * nlevp + q;
+      A.tens.v[gqv] = spheremp * (s3 * A.nm1.v[gqv] + dt2 * vt1);
+      A.tens.v[gqv + 16] = spheremp * (s3 * A.nm1.v[gqv + 16] + dt2 * vt2);
+      A.tens.th[gq] = spheremp * (s3 * A.nm1.th[gq] + dt2 * theta_tens);
+      A.tens.w[gqi] = spheremp * (s3 * A.nm1.w[gqi] + dt2 * w_tens);
+      A.tens.phi[gqi] = spheremp * (s3 * A.nm1.phi[gqi] + dt2 * phi_tens);
+      A.tens.dp[gq] = spheremp * (s3 * A.nm1.dp[gq] - s1 * dt2 * divdp);            // eta_dot = 0
+      if (accum) {
+        sdiv[q] = divdp;
+        A.der.vn0[gqv] += A.eta_ave_w * (v1 * dp);                                  // PA:1190
+        A.der.vn0[gqv + 16] += A.eta_ave_w * (v2 * dp);
+      }
+      if (k == nlev - 1) {                                                          // PA:1349-1361, :1699
+        const double v_gradw_b = v1 * gw1_k1 + v2 * gw2_k1;                         // v_i(nlevp) = v(nlev)
+        const double w_tens_b = (-v_gradw_b) * s1 - s1 * G_GRAV * (1 - mu_k1);
+        A.tens.w[gqi + 16] = spheremp * (s3 * A.nm1.w[gqi + 16] + dt2 * w_tens_b);
+      }
+    }
+    __syncwarp();   // tiles are rewritten by the next iteration
+  }
+
+  // ---- phase 3/4: diagnostic omega (PA:1197-1213, 1312-1313), only when eta_ave_w != 0 ----
+  if (accum) {
+    __syncthreads();
+    if (tid < 16) {
+      double pi_i = A.prm.ptop, om_i = 0.0;
+      for (int k = 0; k < nlev; k++) {
+        const double dp = sdp[k * 16 + tid], dv = sdiv[k * 16 + tid];
+        spnh[k * 16 + tid] = pi_i + dp / 2;                 // pi(k)
+        const double om_next = om_i + dv;
+        sdiv[k * 16 + tid] = (om_i + om_next) / 2;
+        pi_i = pi_i + dp;
+        om_i = om_next;
+      }
+    }
+    __syncthreads();
+    for (int it = 0; it < niter; it++) {
+      const int k = it * KS + kslot;
+      if (k < nlev) {
+        double g1, g2;
+        gradient_sphere(t, spnh + k * 16, g1, g2);
+        const double vgrad_p = sv[k * 32 + p] * g1 + sv[k * 32 + 16 + p] * g2;
+        const double omega = vgrad_p - sdiv[k * 16 + p];
+        A.der.omega_p[(size_t)ie * 16 * nlev + k * 16 + p] += A.eta_ave_w * omega;
+      }
+    }
+  }
+}
+
+void launch_caar_pre(const CaarArgs &A, cudaStream_t st)
+{
+  const size_t sm = caar_smem_bytes(A.prm.nlev);
+  static size_t configured = 0;
+  if (sm > configured) {
+    cudaFuncSetAttribute(caar_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    configured = sm;
+  }
+  caar_pre_kernel<<<A.prm.nelem, CAAR_THREADS, sm, st>>>(A);
+}
+
+// ==========================================================================================
+// DSS (edge_mod.F90:500-629,862-944 + bndry_mod.F90:51-169 as a pull-style node sum), then
+// x rspheremp (PA:1741-1753), surface dpnh_dp_i fix-up (PA:1757-1772), limiter_dp3d_k
+// (PA:1812-1815, 1822-1931).  Reads `tens`, writes the finished state `out` (= np1).
+// ==========================================================================================
+__device__ __forceinline__ double dss_sum(const double *f, size_t estride, size_t off, double own,
+                                          int s0, int s1, int s2)
+{
+  double s = own;
+  if (s0 >= 0) s = s + f[(size_t)(s0 >> 4) * estride + off + (s0 & 15)];
+  if (s1 >= 0) s = s + f[(size_t)(s1 >> 4) * estride + off + (s1 & 15)];
+  if (s2 >= 0) s = s + f[(size_t)(s2 >> 4) * estride + off + (s2 & 15)];
+  return s;
+}
+
+// slow path of limiter_dp3d_k for one element already written to `out`; executed by 16 threads
+__device__ void limiter_columns(const StatePtrs &out, int ie, int nlev, int p, double spheremp,
+                                double dp3d_thresh)
+{
+  double *dp = out.dp + (size_t)ie * 16 * nlev, *th = out.th + (size_t)ie * 16 * nlev;
+  double mn = dp[p] - dp3d_thresh * c_dp0[0];
+  for (int k = 1; k < nlev; k++) mn = fmin(mn, dp[k * 16 + p] - dp3d_thresh * c_dp0[k]);
+  // vtheta_dp -> theta for the whole element (PA:1859), this thread's column
+  for (int k = 0; k < nlev; k++) th[k * 16 + p] = th[k * 16 + p] / dp[k * 16 + p];
+  if (mn < 0) {                                                                     // PA:1863-1893
+    double mass = 0, mass_new = 0;
+    for (int k = 0; k < nlev; k++) mass = mass + (dp[k * 16 + p] - dp3d_thresh * c_dp0[k]) * spheremp;
+    const double sgn = (mass < 0) ? -1.0 : 1.0;
+    for (int k = 0; k < nlev; k++) {
+      double Q = (dp[k * 16 + p] - dp3d_thresh * c_dp0[k]) * spheremp;
+      if (mass < 0) Q = -Q;
+      if (!(Q < 0)) mass_new = mass_new + Q;
+    }
+    for (int k = 0; k < nlev; k++) {
+      double Q = (dp[k * 16 + p] - dp3d_thresh * c_dp0[k]) * spheremp;
+      if (mass < 0) Q = -Q;
+      if (Q < 0) Q = 0;
+      if (mass_new > 0) Q = Q * (fabs(mass) / mass_new);
+      if (sgn < 0) Q = -Q;
+      dp[k * 16 + p] = Q / spheremp + dp3d_thresh * c_dp0[k];
+    }
+  }
+  for (int k = 0; k < nlev; k++) th[k * 16 + p] = th[k * 16 + p] * dp[k * 16 + p];    // PA:1897
+}
+
+
+constexpr int DSS_THREADS = 256;
+
+__global__ void __launch_bounds__(DSS_THREADS) caar_dss_post_kernel(const DssArgs A)
+{
+  const int nlev = A.prm.nlev, nlevp = nlev + 1;
+  const int ie = blockIdx.x, tid = threadIdx.x, p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = DSS_THREADS / 16;
+  const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
+  const int s0 = src[0], s1 = src[1], s2 = src[2];
+  const double rs = A.geo.rspheremp[(size_t)ie * 16 + p];
+  const size_t ev = 32 * (size_t)nlev, em = 16 * (size_t)nlev, ei = 16 * (size_t)nlevp;
+  int lim_dp = 0, lim_th = 0;
+
+  for (int k = kslot; k < nlev; k += KS) {
+    const size_t ov = (size_t)k * 32, om = (size_t)k * 16;
+    const double v1s = dss_sum(A.tens.v, ev, ov, A.tens.v[ie * ev + ov + p], s0, s1, s2);
+    const double v2s = dss_sum(A.tens.v, ev, ov + 16, A.tens.v[ie * ev + ov + 16 + p], s0, s1, s2);
+    const double dps = dss_sum(A.tens.dp, em, om, A.tens.dp[ie * em + om + p], s0, s1, s2);
+    const double ths = dss_sum(A.tens.th, em, om, A.tens.th[ie * em + om + p], s0, s1, s2);
+    const double ws = dss_sum(A.tens.w, ei, om, A.tens.w[ie * ei + om + p], s0, s1, s2);
+    const double phs = dss_sum(A.tens.phi, ei, om, A.tens.phi[ie * ei + om + p], s0, s1, s2);
+    double v1 = rs * v1s, v2 = rs * v2s;
+    const double dp = rs * dps, th = rs * ths;
+    A.out.dp[ie * em + om + p] = dp;
+    A.out.th[ie * em + om + p] = th;
+    A.out.w[ie * ei + om + p] = rs * ws;
+    A.out.phi[ie * ei + om + p] = rs * phs;
+    if (k == nlev - 1) {                                                            // PA:1751-1772
+      const size_t ob = (size_t)nlev * 16;
+      double wb = rs * dss_sum(A.tens.w, ei, ob, A.tens.w[ie * ei + ob + p], s0, s1, s2);
+      const double g1 = A.geo.gradphis[(size_t)ie * 32 + p], g2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
+      const double dpnh = 1 + (((v1 * g1 + v2 * g2) / G_GRAV - wb) / (G_GRAV + (g1 * g1 + g2 * g2) / (2 * G_GRAV))) / A.dt2;
+      wb = wb + A.scale1 * A.dt2 * G_GRAV * (dpnh - 1);
+      v1 = v1 - A.scale1 * A.dt2 * (dpnh - 1) * g1 / 2;
+      v2 = v2 - A.scale1 * A.dt2 * (dpnh - 1) * g2 / 2;
+      A.out.w[ie * ei + ob + p] = wb;
+    }
+    A.out.v[ie * ev + ov + p] = v1;
+    A.out.v[ie * ev + ov + 16 + p] = v2;
+    if (dp < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
+    if (th - A.prm.vtheta_thresh * dp < 0) lim_th = 1;
+  }
+  if (!A.do_limiter) return;
+  // limiter_dp3d_k: rare; block-uniform decision
+  lim_dp = __syncthreads_or(lim_dp);
+  if (lim_dp) {
+    __threadfence_block();
+    if (tid < 16) limiter_columns(A.out, ie, nlev, tid, A.geo.spheremp[(size_t)ie * 16 + tid], A.prm.dp3d_thresh);
+    __threadfence_block();
+    __syncthreads();
+    lim_th = 0;
+    for (int k = kslot; k < nlev; k += KS) {
+      const size_t q = ie * em + (size_t)k * 16 + p;
+      if (A.out.th[q] - A.prm.vtheta_thresh * A.out.dp[q] < 0) lim_th = 1;
+    }
+  }
+  lim_th = __syncthreads_or(lim_th);
+  if (lim_th) {                                                                     // PA:1903-1925
+    for (int k = kslot; k < nlev; k += KS) {
+      const size_t q = ie * em + (size_t)k * 16 + p;
+      const double dp = A.out.dp[q];
+      if (A.out.th[q] - A.prm.vtheta_thresh * dp < 0) A.out.th[q] = A.prm.vtheta_thresh * dp;
+    }
+  }
+}
+
+void launch_caar_dss_post(const DssArgs &A, cudaStream_t st)
+{
+  caar_dss_post_kernel<<<A.prm.nelem, DSS_THREADS, 0, st>>>(A);
+}
+
+// ==========================================================================================
+// compute_stage_value_dirk (IM:60-364): per-column Newton solve, one CTA per element.
+// (k,p)-parallel phases for EOS / residual / update, the tridiagonal recurrence (IM:576-599)
+// runs on one warp; convergence is decided per element as in IM:330-335.
+// ==========================================================================================
+
+constexpr int DIRK_THREADS = 256;
+constexpr int DIRK_ARRAYS = 12;
+
+__host__ __device__ inline size_t dirk_smem_bytes(int nlev)
+{
+  return sizeof(double) * 16 * ((size_t)DIRK_ARRAYS * nlev + 2) + 64 * sizeof(double);
+}
+
+__device__ __forceinline__ double block_max(double v, double *red, int tid)
+{
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  __syncthreads();
+  if ((tid & 31) == 0) red[tid >> 5] = v;
+  __syncthreads();
+  double r = red[0];
+  for (int i = 1; i < DIRK_THREADS / 32; i++) r = fmax(r, red[i]);
+  return r;
+}
+
+// IM:42-53 at interface k (1 <= k < nlev), state arrays of one element in global memory
+__device__ __forceinline__ double gwphis_at(const double *v, const double *dp, int k, int p,
+                                            double g1, double g2)
+{
+  const double dk = dp[k * 16 + p], dm = dp[(k - 1) * 16 + p];
+  const double vi1 = (dk * v[k * 32 + p] + dm * v[(k - 1) * 32 + p]) / (dk + dm);
+  const double vi2 = (dk * v[k * 32 + 16 + p] + dm * v[(k - 1) * 32 + 16 + p]) / (dk + dm);
+  return (vi1 * g1 + vi2 * g2) * c_hybi[k];
+}
+
+__global__ void __launch_bounds__(DIRK_THREADS) dirk_kernel(const DirkArgs A)
+{
+  extern __shared__ double smem[];
+  const int nlev = A.prm.nlev, nlevp = nlev + 1;
+  const int ie = blockIdx.x, tid = threadIdx.x, n16 = 16 * nlev;
+  double *sdp = smem, *sth = sdp + n16, *sdphi0 = sth + n16, *sw0 = sdphi0 + n16, *sphi0 = sw0 + n16;
+  double *sw = sphi0 + n16 + 16;           // phi0 has nlevp tiles (bottom = phis)
+  double *sdphi = sw + n16, *spnh = sdphi + n16, *sx = spnh + n16, *sb = sx + n16, *sc = sb + n16;
+  double *sD = sc + n16;                   // modified diagonal / reciprocal
+  double *red = sD + n16 + 16;
+  const double g = G_GRAV, dt2 = A.dt2;
+  const double ptop = A.prm.ptop;
+
+  const double *gth = A.np1.th + (size_t)ie * n16, *gdp = A.np1.dp + (size_t)ie * n16;
+  const double *gv = A.np1.v + (size_t)ie * 2 * n16;
+  double *gw = A.np1.w + (size_t)ie * 16 * nlevp, *gphi = A.np1.phi + (size_t)ie * 16 * nlevp;
+  const double gp1 = A.geo.gradphis[(size_t)ie * 32 + (tid & 15)], gp2 = A.geo.gradphis[(size_t)ie * 32 + 16 + (tid & 15)];
+  int bad = 0;
+
+  // ---- load, wmax (IM:168-170) ----
+  double wmax = 0.0;
+  for (int q = tid; q < n16; q += DIRK_THREADS) {
+    sdp[q] = gdp[q]; sth[q] = gth[q];
+    const double w = gw[q];
+    sw0[q] = w; sphi0[q] = gphi[q];
+    wmax = fmax(wmax, fabs(w));
+  }
+  if (tid < 16) { sphi0[n16 + tid] = gphi[n16 + tid]; wmax = fmax(wmax, fabs(gw[n16 + tid])); }
+  wmax = fmax(1.0, block_max(wmax, red, tid));
+
+  // ---- explicit stiff terms of earlier stages (IM:176-205) ----
+  for (int pass = 0; pass < 2; pass++) {
+    const double dt3 = pass == 0 ? A.alphadt_n0 : A.alphadt_nm1;
+    if (dt3 == 0.0) continue;
+    const StatePtrs &S = pass == 0 ? A.n0 : A.nm1;
+    const double *tth = S.th + (size_t)ie * n16, *tdp = S.dp + (size_t)ie * n16;
+    const double *tphi = S.phi + (size_t)ie * 16 * nlevp, *tw = S.w + (size_t)ie * 16 * nlevp;
+    const double *tv = S.v + (size_t)ie * 2 * n16;
+    for (int q = tid; q < n16; q += DIRK_THREADS) {
+      const double dphi = tphi[q + 16] - tphi[q], th = tth[q], dp = tdp[q];
+      if (th < 0 || dp < 0 || dphi > 0) bad = 1;
+      spnh[q] = eos_pnh(RGAS * th / (-dphi));
+    }
+    __syncthreads();
+    for (int q = tid; q < n16; q += DIRK_THREADS) {
+      const int k = q >> 4, p = q & 15;
+      double mu;
+      if (k == 0) mu = 2 * (spnh[q] - ptop) / tdp[q];
+      else mu = (spnh[q] - spnh[q - 16]) / ((tdp[q] + tdp[q - 16]) / 2);
+      sw0[q] = sw0[q] + dt3 * g * (mu - 1);
+      const double gwh = (k == 0) ? 0.0 : gwphis_at(tv, tdp, k, p, gp1, gp2);
+      sphi0[q] = sphi0[q] + dt3 * g * tw[q] - dt3 * gwh;
+    }
+    __syncthreads();
+  }
+  // ---- wphis(np1) term (IM:208-211), Jacobian coefficient b (IM:416,422,430) ----
+  {
+    const double a = (dt2 * g) * (dt2 * g) / (1 - KAPPA);
+    for (int q = tid; q < n16; q += DIRK_THREADS) {
+      const int k = q >> 4, p = q & 15;
+      const double gwh = (k == 0) ? 0.0 : gwphis_at(gv, gdp, k, p, gp1, gp2);
+      sphi0[q] = sphi0[q] - dt2 * gwh;
+      sb[q] = (k == 0) ? a / sdp[q] : 2 * a / (sdp[q - 16] + sdp[q]);
+    }
+  }
+  __syncthreads();
+  // ---- hydrostatic initial guess phi_from_eos (EOS:286-302, IM:228-230) ----
+  // sx <- Rgas*vtheta_dp*(p/p0)^(kappa-1)/p0 needs the pressure scan first
+  if (tid < 16) {
+    double p_i = ptop;
+    for (int k = 0; k < nlev; k++) { const double pn = p_i + sdp[k * 16 + tid]; sc[k * 16 + tid] = (pn + p_i) / 2; p_i = pn; }
+  }
+  __syncthreads();
+  for (int q = tid; q < n16; q += DIRK_THREADS)
+    sx[q] = (RGAS * sth[q] * pow(sc[q] / P0, KAPPA - 1)) / P0;
+  __syncthreads();
+  if (tid < 16) {   // sD <- phi_np1 (hydrostatic), bottom-up
+    double ph = sphi0[n16 + tid];
+    for (int k = nlev - 1; k >= 0; k--) { ph = ph + sx[k * 16 + tid]; sD[k * 16 + tid] = ph; }
+  }
+  __syncthreads();
+  int nsafe = 0;
+  for (int q = tid; q < n16; q += DIRK_THREADS) {                                   // IM:234-253
+    const double below = (q + 16 < n16) ? sD[q + 16] : sphi0[q + 16];
+    double dphi = below - sD[q];
+    sdphi0[q] = sphi0[q + 16] - sphi0[q];
+    if (dphi > -g) { dphi = -g; nsafe = 1; }
+    sdphi[q] = dphi;
+  }
+  nsafe = __syncthreads_or(nsafe);
+  if (nsafe) {                                                                      // IM:254-260
+    if (tid < 16) {
+      double ph = sphi0[n16 + tid];
+      for (int k = nlev - 1; k >= 0; k--) { ph = ph - sdphi[k * 16 + tid]; sD[k * 16 + tid] = ph; }
+    }
+    __syncthreads();
+  }
+  for (int q = tid; q < n16; q += DIRK_THREADS) {
+    sw[q] = (sD[q] - sphi0[q]) / (dt2 * g);
+    const double th = sth[q], dp = sdp[q], dphi = sdphi[q];
+    if (th < 0 || dp < 0 || dphi > 0) bad = 1;
+    spnh[q] = eos_pnh(RGAS * th / (-dphi));                                         // IM:261
+  }
+  __syncthreads();
+
+  // ---- Newton iteration (IM:268-336) ----
+  int itercount = 0;
+  double deltaerr = 0.0;
+  const int maxiter = 20;
+  while (itercount < maxiter) {
+    // residual Fn (IM:263-264 / 326), x = -Fn, c = pnh/dphi
+    for (int q = tid; q < n16; q += DIRK_THREADS) {
+      const int k = q >> 4;
+      double mu;
+      if (k == 0) mu = 2 * (spnh[q] - ptop) / sdp[q];
+      else mu = (spnh[q] - spnh[q - 16]) / ((sdp[q] + sdp[q - 16]) / 2);
+      const double Fn = sw[q] - (sw0[q] + g * dt2 * (mu - 1));
+      sx[q] = -Fn;
+      sc[q] = spnh[q] / sdphi[q];
+    }
+    __syncthreads();
+    // tridiagonal solve (IM:414-433 assembled on the fly, IM:590-598)
+    if (tid < 16) {
+      const int p = tid;
+      double U = 2 * sb[p] * sc[p];
+      double D = 1 - U;
+      double x = sx[p];
+      sD[p] = D;
+      for (int k = 0; k < nlev - 1; k++) {
+        const int q1 = (k + 1) * 16 + p;
+        const double b1 = sb[q1];
+        const double L = b1 * sc[q1 - 16];
+        const double U1 = b1 * sc[q1];
+        const double D1raw = (k + 1 < nlev - 1) ? (1 - L - U1) : (1 - L - U1);
+        const double dlk = L / D;
+        D = D1raw - dlk * U;
+        x = sx[q1] - dlk * x;
+        sx[q1] = x;
+        sD[q1] = D;
+        U = U1;
+      }
+      x = x / D;
+      sx[(nlev - 1) * 16 + p] = x;
+      for (int k = nlev - 2; k >= 0; k--) {
+        const int q = k * 16 + p;
+        const double Uk = (k == 0) ? 2 * sb[q] * sc[q] : sb[q] * sc[q];
+        x = (sx[q] - Uk * x) / sD[q];
+        sx[q] = x;
+      }
+    }
+    __syncthreads();
+    // dphi update (IM:278-283) and positivity check
+    int anypos = 0;
+    for (int q = tid; q < n16; q += DIRK_THREADS) {
+      double dphi;
+      if (q + 16 < n16) dphi = sdphi0[q] + dt2 * g * ((sw[q + 16] - sw[q]) + (sx[q + 16] - sx[q]));
+      else dphi = sdphi0[q] - dt2 * g * (sw[q] + sx[q]);
+      sdphi[q] = dphi;
+      if (dphi >= 0) anypos = 1;
+    }
+    anypos = __syncthreads_or(anypos);
+    if (anypos) {                                                                   // IM:285-319 (rare)
+      if (tid < 16) {
+        const int p = tid;
+        int colpos = 0;
+        for (int k = 0; k < nlev; k++) if (sdphi[k * 16 + p] >= 0) colpos = 1;
+        double alpha = 1.0;
+        if (colpos) {
+          for (int k = 0; k < nlev; k++) {
+            double dx, dw;
+            if (k < nlev - 1) { dx = sx[(k + 1) * 16 + p] - sx[k * 16 + p]; dw = sw[(k + 1) * 16 + p] - sw[k * 16 + p]; }
+            else { dx = -sx[k * 16 + p]; dw = -sw[k * 16 + p]; }
+            if (dx != 0) {
+              const double alpha_k = -(sdphi0[k * 16 + p] + dt2 * g * dw) / (dt2 * g * dx);
+              if (alpha_k >= 0) alpha = fmin(alpha, alpha_k);
+            }
+          }
+          alpha = alpha / 2;
+          for (int k = 0; k < nlev - 1; k++)
+            sdphi[k * 16 + p] = sdphi0[k * 16 + p] + dt2 * g * ((sw[(k + 1) * 16 + p] - sw[k * 16 + p]) + alpha * (sx[(k + 1) * 16 + p] - sx[k * 16 + p]));
+          sdphi[(nlev - 1) * 16 + p] = sdphi0[(nlev - 1) * 16 + p] - dt2 * g * (sw[(nlev - 1) * 16 + p] + alpha * sx[(nlev - 1) * 16 + p]);
+        }
+        red[32 + p] = alpha;
+      }
+      __syncthreads();
+    }
+    double xmax = 0.0;
+    for (int q = tid; q < n16; q += DIRK_THREADS) {
+      const double x = sx[q];
+      const double alpha = anypos ? red[32 + (q & 15)] : 1.0;
+      sw[q] = sw[q] + alpha * x;                                                    // IM:320-322
+      xmax = fmax(xmax, fabs(x));
+      const double th = sth[q], dp = sdp[q], dphi = sdphi[q];
+      if (th < 0 || dp < 0 || dphi > 0) bad = 1;
+      spnh[q] = eos_pnh(RGAS * th / (-dphi));                                       // IM:324
+    }
+    xmax = block_max(xmax, red, tid);   // contains the barriers that publish sw/spnh
+    deltaerr = xmax / wmax;                                                         // IM:330
+    itercount++;
+    if (deltaerr < 1.0e-11) break;                                                  // IM:335
+  }
+  // ---- phi update (IM:339) and write back ----
+  for (int q = tid; q < n16; q += DIRK_THREADS) {
+    const double w = sw[q];
+    gw[q] = w;
+    gphi[q] = sphi0[q] + dt2 * g * w;
+  }
+  if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
+  if (tid == 0) {
+    atomicMax(A.max_iter, itercount);
+    atomicMax(A.max_deltaerr_bits, (unsigned long long)__double_as_longlong(deltaerr));
+    if (itercount >= maxiter) atomicOr(A.err, ERR_DIRK_NOT_CONVERGED);
+  }
+}
+
+void launch_dirk(const DirkArgs &A, cudaStream_t st)
+{
+  const size_t sm = dirk_smem_bytes(A.prm.nlev);
+  static size_t configured = 0;
+  if (sm > configured) {
+    cudaFuncSetAttribute(dirk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    configured = sm;
+  }
+  dirk_kernel<<<A.prm.nelem, DIRK_THREADS, sm, st>>>(A);
+}
+
+// ==========================================================================================
+// Hyperviscosity (PA:546-862, VT:39-169).  Weak-form operators (DM:453-580, 784-858, 1072-1251).
+// ==========================================================================================
+struct PtW {                 // extra per-point data of the weak operators
+  double dta[4], dtb[4];     // Dvv(a,j), Dvv(b,j)
+  double mpa[4], mpb[4];     // mp(j,b) , mp(a,j)
+  double metinv[4];          // index b2*2+a2
+  double spheremp;
+  double lrf2;               // laplacian_rigid_factor^2
+};
+
+__device__ __forceinline__ void ptw_init(PtW &w, const Pt &t, const Geo &g, int ie, double lrf)
+{
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    w.dta[j] = c_dvv[j * 4 + t.a]; w.dtb[j] = c_dvv[j * 4 + t.b];
+    w.mpa[j] = c_mp[t.b * 4 + j]; w.mpb[j] = c_mp[j * 4 + t.a];
+  }
+#pragma unroll
+  for (int q = 0; q < 4; q++) w.metinv[q] = g.metinv[(size_t)ie * 64 + q * 16 + t.p];
+  w.spheremp = g.spheremp[(size_t)ie * 16 + t.p];
+  w.lrf2 = lrf * lrf;
+}
+
+constexpr int HV_THREADS = 256;
+constexpr int HV_SLOTS = 18;
+
+// Laplacians of the six fields of one level (scalar: DM:1072-1119 with var_coef=.false.;
+// vector: DM:1212-1251).  All 16 lanes of the half-warp must call this together.
+// scr: HV_SLOTS tiles private to the half-warp.
+__device__ __forceinline__ void laplace_level(const Pt &t, const PtW &w, double *scr, double nu_ratio,
+                                              const double s_in[4], double v1, double v2,
+                                              double lap_s[4], double &lap_v1, double &lap_v2)
+{
+  const int p = t.p;
+  double gv1, gv2, vc1, vc2;
+  div_prep(t, v1, v2, gv1, gv2);
+  vort_prep(t, v1, v2, vc1, vc2);
+#pragma unroll
+  for (int f = 0; f < 4; f++) scr[f * 16 + p] = s_in[f];
+  scr[4 * 16 + p] = gv1; scr[5 * 16 + p] = gv2; scr[6 * 16 + p] = vc1; scr[7 * 16 + p] = vc2;
+  __syncwarp();
+#pragma unroll
+  for (int f = 0; f < 4; f++) {
+    double g1, g2;
+    gradient_sphere(t, scr + f * 16, g1, g2);
+    // divergence_sphere_wk first half DM:814-819, times spheremp
+    scr[(8 + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[0] * g1 + t.Dinv[2] * g2);
+    scr[(9 + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[1] * g1 + t.Dinv[3] * g2);
+  }
+  const double div = nu_ratio * div_finish(t, scr + 4 * 16, scr + 5 * 16);
+  const double vor = vort_finish(t, scr + 6 * 16, scr + 7 * 16);
+  scr[16 * 16 + p] = div;
+  scr[17 * 16 + p] = vor;
+  __syncwarp();
+#pragma unroll
+  for (int f = 0; f < 4; f++) {                                                     // DM:821-833
+    const double *T1 = scr + (8 + 2 * f) * 16 + t.b * 4, *T2 = scr + (9 + 2 * f) * 16 + t.a;
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc = acc - (T1[j] * w.dta[j] + T2[4 * j] * w.dtb[j]) * t.sfi;
+    lap_s[f] = acc;
+  }
+  {
+    const double *sd_r = scr + 16 * 16 + t.b * 4, *sd_c = scr + 16 * 16 + t.a;      // div(j,b), div(a,j)
+    const double *sv_r = scr + 17 * 16 + t.b * 4, *sv_c = scr + 17 * 16 + t.a;
+    double gc1 = 0.0, gc2 = 0.0, cc1 = 0.0, cc2 = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      // gradient_sphere_wk_testcov DM:555-569
+      gc1 = gc1 - ((w.mpa[j] * w.metinv[0] * t.metdet * sd_r[j] * w.dta[j]) + (w.mpb[j] * w.metinv[1] * t.metdet * sd_c[4 * j] * w.dtb[j]));
+      gc2 = gc2 - ((w.mpa[j] * w.metinv[2] * t.metdet * sd_r[j] * w.dta[j]) + (w.mpb[j] * w.metinv[3] * t.metdet * sd_c[4 * j] * w.dtb[j]));
+      // curl_sphere_wk_testcov DM:493-503
+      cc1 = cc1 - (w.mpb[j] * sv_c[4 * j] * w.dtb[j]);
+      cc2 = cc2 + (w.mpa[j] * sv_r[j] * w.dta[j]);
+    }
+    const double gr1 = (t.D[0] * gc1 + t.D[2] * gc2) * t.sfi, gr2 = (t.D[1] * gc1 + t.D[3] * gc2) * t.sfi;
+    const double cu1 = (t.D[0] * cc1 + t.D[2] * cc2) * t.sfi, cu2 = (t.D[1] * cc1 + t.D[3] * cc2) * t.sfi;
+    lap_v1 = (gr1 - cu1) + 2 * w.spheremp * v1 * w.lrf2;                              // DM:1241-1247
+    lap_v2 = (gr2 - cu2) + 2 * w.spheremp * v2 * w.lrf2;
+  }
+  __syncwarp();
+}
+
+
+__host__ __device__ inline size_t hv_smem_bytes() { return sizeof(double) * (HV_THREADS / 16) * HV_SLOTS * 16; }
+
+// pass 1 (PA:629-636 + VT:93-107): laplacians of (state - reference state) -> tout
+__global__ void __launch_bounds__(HV_THREADS) hv_laplace1_kernel(const HvArgs A)
+{
+  extern __shared__ double smem[];
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = HV_THREADS / 16;
+  double *scr = smem + kslot * (HV_SLOTS * 16);
+  Pt t; PtW w;
+  pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
+  ptw_init(w, t, A.geo, ie, A.prm.rearth_inv);
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  const int niter = (nlev + KS - 1) / KS;
+  for (int it = 0; it < niter; it++) {
+    const int kk = it * KS + kslot;
+    const bool act = kk < nlev;
+    const int k = act ? kk : nlev - 1, q = k * 16 + p;
+    const double dp = A.st.dp[em + q];
+    const double theta = A.th_is_theta ? A.st.th[em + q] : A.st.th[em + q] / dp;     // PA:615-621
+    double s[4], lap[4], l1, l2;
+    s[0] = dp - A.ref.dp_ref[em + q];
+    s[1] = theta - A.ref.theta_ref[em + q];
+    s[2] = A.st.w[ei + q];
+    s[3] = A.st.phi[ei + q] - A.ref.phi_ref[ei + q];
+    const double v1 = A.st.v[ev + k * 32 + p], v2 = A.st.v[ev + k * 32 + 16 + p];
+    laplace_level(t, w, scr, A.nu_ratio, s, v1, v2, lap, l1, l2);
+    if (act) {
+      A.tout.dp[em + q] = lap[0]; A.tout.th[em + q] = lap[1];
+      A.tout.w[ei + q] = lap[2]; A.tout.phi[ei + q] = lap[3];
+      A.tout.v[ev + k * 32 + p] = l1; A.tout.v[ev + k * 32 + 16 + p] = l2;
+    }
+  }
+}
+
+// pass 2 (VT:134-164 + PA:657-663): DSS(tin) * rspheremp -> laplacian again -> * (-nu) -> tout
+__global__ void __launch_bounds__(HV_THREADS) hv_laplace2_kernel(const HvArgs A)
+{
+  extern __shared__ double smem[];
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = HV_THREADS / 16;
+  double *scr = smem + kslot * (HV_SLOTS * 16);
+  Pt t; PtW w;
+  pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
+  ptw_init(w, t, A.geo, ie, A.prm.rearth_inv);
+  const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
+  const int s0 = src[0], s1 = src[1], s2 = src[2];
+  const double rs = A.geo.rspheremp[(size_t)ie * 16 + p];
+  const size_t sm_ = 16 * (size_t)nlev, si = 16 * (size_t)nlevp, sv = 32 * (size_t)nlev;
+  const size_t em = ie * sm_, ei = ie * si, ev = ie * sv;
+  const int niter = (nlev + KS - 1) / KS;
+  for (int it = 0; it < niter; it++) {
+    const int kk = it * KS + kslot;
+    const bool act = kk < nlev;
+    const int k = act ? kk : nlev - 1, q = k * 16 + p;
+    const size_t om = (size_t)k * 16, ov = (size_t)k * 32;
+    double s[4], lap[4], l1, l2;
+    s[0] = rs * dss_sum(A.tin.dp, sm_, om, A.tin.dp[em + q], s0, s1, s2);
+    s[1] = rs * dss_sum(A.tin.th, sm_, om, A.tin.th[em + q], s0, s1, s2);
+    s[2] = rs * dss_sum(A.tin.w, si, om, A.tin.w[ei + q], s0, s1, s2);
+    s[3] = rs * dss_sum(A.tin.phi, si, om, A.tin.phi[ei + q], s0, s1, s2);
+    const double v1 = rs * dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2);
+    const double v2 = rs * dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2);
+    laplace_level(t, w, scr, A.nu_ratio, s, v1, v2, lap, l1, l2);
+    if (act) {
+      A.tout.dp[em + q] = -A.prm.nu_p * lap[0]; A.tout.th[em + q] = -A.prm.nu * lap[1];
+      A.tout.w[ei + q] = -A.prm.nu * lap[2]; A.tout.phi[ei + q] = -A.prm.nu_s * lap[3];
+      A.tout.v[ev + ov + p] = -A.prm.nu * l1; A.tout.v[ev + ov + 16 + p] = -A.prm.nu * l2;
+    }
+  }
+}
+
+// pass 3 (PA:674-758, 767-774): DSS(tin) * dt * rspheremp added to the state
+__global__ void __launch_bounds__(HV_THREADS) hv_update_kernel(const HvArgs A)
+{
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = HV_THREADS / 16;
+  const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
+  const int s0 = src[0], s1 = src[1], s2 = src[2];
+  const double rs = A.geo.rspheremp[(size_t)ie * 16 + p], dt = A.dt;
+  const size_t sm_ = 16 * (size_t)nlev, si = 16 * (size_t)nlevp, sv = 32 * (size_t)nlev;
+  const size_t em = ie * sm_, ei = ie * si, ev = ie * sv;
+  for (int k = kslot; k < nlev; k += KS) {
+    const int q = k * 16 + p;
+    const size_t om = (size_t)k * 16, ov = (size_t)k * 32;
+    const double tdp = dt * dss_sum(A.tin.dp, sm_, om, A.tin.dp[em + q], s0, s1, s2) * rs;
+    const double tth = dt * dss_sum(A.tin.th, sm_, om, A.tin.th[em + q], s0, s1, s2) * rs;
+    const double tw = dt * dss_sum(A.tin.w, si, om, A.tin.w[ei + q], s0, s1, s2) * rs;
+    const double tph = dt * dss_sum(A.tin.phi, si, om, A.tin.phi[ei + q], s0, s1, s2) * rs;
+    const double tv1 = dt * dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2) * rs;
+    const double tv2 = dt * dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2) * rs;
+    const double dp_old = A.st.dp[em + q];
+    const double theta_old = A.th_is_theta ? A.st.th[em + q] : A.st.th[em + q] / dp_old;
+    // remove/add reference state exactly as PA:629-647 does (rounding of (x-r)+r)
+    const double dref = A.ref.dp_ref[em + q], tref = A.ref.theta_ref[em + q], pref = A.ref.phi_ref[ei + q];
+    const double dp_new = ((dp_old - dref) + dref) + tdp;
+    const double theta_new = ((theta_old - tref) + tref) + tth;
+    const double v1 = A.st.v[ev + ov + p] + tv1, v2 = A.st.v[ev + ov + 16 + p] + tv2;
+    A.st.v[ev + ov + p] = v1; A.st.v[ev + ov + 16 + p] = v2;
+    A.st.w[ei + q] = A.st.w[ei + q] + tw;
+    A.st.dp[em + q] = dp_new;
+    A.st.phi[ei + q] = ((A.st.phi[ei + q] - pref) + pref) + tph;
+    A.st.th[em + q] = A.last_subcycle ? theta_new * dp_new : theta_new;
+    if (A.last_subcycle && k == nlev - 1) {
+      const double g1 = A.geo.gradphis[(size_t)ie * 32 + p], g2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
+      A.st.w[ei + (size_t)nlev * 16 + p] = (v1 * g1 + v2 * g2) / G_GRAV;
+    }
+  }
+}
+
+// sponge pass A (PA:784-800): xfac * laplacian of the top nlev_tom levels of the state -> tout
+__global__ void __launch_bounds__(HV_THREADS) hv_sponge_laplace_kernel(const HvArgs A)
+{
+  extern __shared__ double smem[];
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = blockIdx.x, tid = threadIdx.x;
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = HV_THREADS / 16;
+  double *scr = smem + kslot * (HV_SLOTS * 16);
+  Pt t; PtW w;
+  pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
+  ptw_init(w, t, A.geo, ie, A.prm.rearth_inv);
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  const int niter = (ntom + KS - 1) / KS;
+  for (int it = 0; it < niter; it++) {
+    const int kk = it * KS + kslot;
+    const bool act = kk < ntom;
+    const int k = act ? kk : ntom - 1, q = k * 16 + p;
+    double s[4], lap[4], l1, l2;
+    s[0] = A.st.dp[em + q]; s[1] = A.st.th[em + q]; s[2] = A.st.w[ei + q]; s[3] = A.st.phi[ei + q];
+    const double v1 = A.st.v[ev + k * 32 + p], v2 = A.st.v[ev + k * 32 + 16 + p];
+    laplace_level(t, w, scr, 1.0, s, v1, v2, lap, l1, l2);
+    if (act) {
+      const double xfac = A.dt * c_nu_scale_top[k] * A.prm.nu_top;                    // PA:793
+      A.tout.dp[em + q] = xfac * lap[0]; A.tout.th[em + q] = xfac * lap[1];
+      A.tout.w[ei + q] = xfac * lap[2]; A.tout.phi[ei + q] = xfac * lap[3];
+      A.tout.v[ev + k * 32 + p] = xfac * l1; A.tout.v[ev + k * 32 + 16 + p] = xfac * l2;
+    }
+  }
+}
+
+// sponge pass B (PA:820-852): state += DSS(tin) * rspheremp on the top nlev_tom levels
+__global__ void __launch_bounds__(HV_THREADS) hv_sponge_update_kernel(const HvArgs A)
+{
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = blockIdx.x, tid = threadIdx.x;
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = HV_THREADS / 16;
+  const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
+  const int s0 = src[0], s1 = src[1], s2 = src[2];
+  const double rs = A.geo.rspheremp[(size_t)ie * 16 + p];
+  const size_t sm_ = 16 * (size_t)nlev, si = 16 * (size_t)nlevp, sv = 32 * (size_t)nlev;
+  const size_t em = ie * sm_, ei = ie * si, ev = ie * sv;
+  for (int k = kslot; k < ntom; k += KS) {
+    const int q = k * 16 + p;
+    const size_t om = (size_t)k * 16, ov = (size_t)k * 32;
+    A.st.v[ev + ov + p] += dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2) * rs;
+    A.st.v[ev + ov + 16 + p] += dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2) * rs;
+    A.st.w[ei + q] += dss_sum(A.tin.w, si, om, A.tin.w[ei + q], s0, s1, s2) * rs;
+    A.st.dp[em + q] += dss_sum(A.tin.dp, sm_, om, A.tin.dp[em + q], s0, s1, s2) * rs;
+    A.st.phi[ei + q] += dss_sum(A.tin.phi, si, om, A.tin.phi[ei + q], s0, s1, s2) * rs;
+    A.st.th[em + q] += dss_sum(A.tin.th, sm_, om, A.tin.th[em + q], s0, s1, s2) * rs;
+  }
+}
+
+void launch_hv(int which, const HvArgs &A, cudaStream_t st)
+{
+  const size_t sm = hv_smem_bytes();
+  switch (which) {
+    case 0: hv_laplace1_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
+    case 1: hv_laplace2_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
+    case 2: hv_update_kernel<<<A.prm.nelem, HV_THREADS, 0, st>>>(A); break;
+    case 3: hv_sponge_laplace_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
+    case 4: hv_sponge_update_kernel<<<A.prm.nelem, HV_THREADS, 0, st>>>(A); break;
+  }
+}
+
+// ==========================================================================================
+// Small element-wise kernels of prim_advance_exp (PA:140-143, 197-208, 313-326)
+// ==========================================================================================
+
+__global__ void __launch_bounds__(DSS_THREADS) combo_kernel(const ComboArgs A)
+{
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = DSS_THREADS / 16;
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  int lim_dp = 0, lim_th = 0;
+  for (int k = kslot; k < nlevp; k += KS) {
+    const int q = k * 16 + p;
+    if (A.kind == 9) {
+      A.a.w[ei + q] = A.a.w[ei + q] + (A.b.w[ei + q] - A.c.w[ei + q]) / 4;
+      if (k < nlev) {
+        const size_t qv = ev + k * 32 + p;
+        A.a.v[qv] = A.a.v[qv] + (A.b.v[qv] - A.c.v[qv]) / 4;
+        A.a.v[qv + 16] = A.a.v[qv + 16] + (A.b.v[qv + 16] - A.c.v[qv + 16]) / 4;
+        const double th = A.a.th[em + q] + (A.b.th[em + q] - A.c.th[em + q]) / 4;
+        const double dp = A.a.dp[em + q] + (A.b.dp[em + q] - A.c.dp[em + q]) / 4;
+        A.a.th[em + q] = th; A.a.dp[em + q] = dp;
+        A.a.phi[ei + q] = A.a.phi[ei + q] + (A.b.phi[ei + q] - A.c.phi[ei + q]) / 4;
+        if (dp < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
+        if (th - A.prm.vtheta_thresh * dp < 0) lim_th = 1;
+      }
+    } else {
+      A.a.w[ei + q] = (5 * A.a.w[ei + q] - A.b.w[ei + q]) / 4;
+      if (k < nlev) {
+        const size_t qv = ev + k * 32 + p;
+        A.a.v[qv] = (5 * A.a.v[qv] - A.b.v[qv]) / 4;
+        A.a.v[qv + 16] = (5 * A.a.v[qv + 16] - A.b.v[qv + 16]) / 4;
+        A.a.th[em + q] = (5 * A.a.th[em + q] - A.b.th[em + q]) / 4;
+        A.a.dp[em + q] = (5 * A.a.dp[em + q] - A.b.dp[em + q]) / 4;
+        A.a.phi[ei + q] = (5 * A.a.phi[ei + q] - A.b.phi[ei + q]) / 4;
+      }
+    }
+  }
+  if (A.kind != 9) return;
+  lim_dp = __syncthreads_or(lim_dp);                                                // PA:324-325
+  if (lim_dp) {
+    __threadfence_block();
+    if (tid < 16) limiter_columns(A.a, ie, nlev, tid, A.geo.spheremp[(size_t)ie * 16 + tid], A.prm.dp3d_thresh);
+    __threadfence_block();
+    __syncthreads();
+    lim_th = 0;
+    for (int k = kslot; k < nlev; k += KS) {
+      const size_t q = em + (size_t)k * 16 + p;
+      if (A.a.th[q] - A.prm.vtheta_thresh * A.a.dp[q] < 0) lim_th = 1;
+    }
+  }
+  lim_th = __syncthreads_or(lim_th);
+  if (lim_th) {
+    for (int k = kslot; k < nlev; k += KS) {
+      const size_t q = em + (size_t)k * 16 + p;
+      const double dp = A.a.dp[q];
+      if (A.a.th[q] - A.prm.vtheta_thresh * dp < 0) A.a.th[q] = A.prm.vtheta_thresh * dp;
+    }
+  }
+}
+
+void launch_combo(const ComboArgs &A, cudaStream_t st)
+{
+  combo_kernel<<<A.prm.nelem, DSS_THREADS, 0, st>>>(A);
+}
+
+// PA:140-143  w_i(nlevp,n0) = (v(nlev) . gradphis)/g
+__global__ void wbc_kernel(StatePtrs s, Geo geo, int nelem, int nlev)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nelem * 16) return;
+  const int ie = i >> 4, p = i & 15;
+  const double *v = s.v + (size_t)ie * 32 * nlev + (nlev - 1) * 32;
+  s.w[(size_t)ie * 16 * (nlev + 1) + nlev * 16 + p] =
+      (v[p] * geo.gradphis[(size_t)ie * 32 + p] + v[16 + p] * geo.gradphis[(size_t)ie * 32 + 16 + p]) / G_GRAV;
+}
+
+void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st)
+{
+  wbc_kernel<<<(nelem * 16 + 255) / 256, 256, 0, st>>>(s, geo, nelem, nlev);
+}
+
+}  // namespace thetal

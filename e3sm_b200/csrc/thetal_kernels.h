@@ -1,0 +1,62 @@
+// Kernel argument blocks and launchers of libthetal_b200.so (kernels in thetal_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include "thetal_ctx.h"
+
+namespace thetal {
+
+struct CaarArgs {
+  StatePtrs n0, nm1, tens;
+  Geo geo;
+  Derived der;
+  Params prm;
+  double dt2, eta_ave_w, scale1, scale2, scale3;
+  int *err;
+};
+
+struct DssArgs {
+  StatePtrs tens, out;
+  Geo geo;
+  Params prm;
+  double dt2, scale1, scale3;
+  int do_limiter;
+};
+
+struct DirkArgs {
+  StatePtrs np1, n0, nm1;
+  Geo geo;
+  Params prm;
+  double dt2, alphadt_n0, alphadt_nm1;
+  int *err;
+  int *max_iter;            // running max of itercount over elements (atomicMax)
+  unsigned long long *max_deltaerr_bits;   // running max of deltaerr (as ordered bits)
+};
+
+struct HvArgs {
+  StatePtrs st;             // state at time level nt (in/out)
+  StatePtrs tin, tout;      // tens buffers (gather source / destination)
+  Geo geo;
+  RefStates ref;
+  Params prm;
+  double dt, nu_ratio;
+  int th_is_theta;          // st.th currently holds theta (not vtheta_dp)
+  int last_subcycle;        // convert back to vtheta_dp and reset w b.c. (PA:767-774)
+};
+
+struct ComboArgs {
+  StatePtrs a, b, c;     // tt9: a(np1) += (b(nm1) - c(n0))/4 ; tt5: a(nm1) = (5*a - b(n0))/4
+  Geo geo;
+  Params prm;
+  int kind;              // 9 or 5
+};
+
+void upload_constants(const double *dvv, const double *mp, const double *hybi, const double *dp0,
+                      const double *nu_scale_top, int nlev);
+void launch_caar_pre(const CaarArgs &A, cudaStream_t st);
+void launch_caar_dss_post(const DssArgs &A, cudaStream_t st);
+void launch_dirk(const DirkArgs &A, cudaStream_t st);
+void launch_hv(int which, const HvArgs &A, cudaStream_t st);   // 0 laplace1, 1 laplace2, 2 update, 3 sponge laplace, 4 sponge update
+void launch_combo(const ComboArgs &A, cudaStream_t st);
+void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st);
+
+}  // namespace thetal

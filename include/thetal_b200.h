@@ -1,0 +1,137 @@
+/* C ABI of libthetal_b200.so -- B200-native theta-l nonhydrostatic dycore step.
+ *
+ * The first group re-exports, symbol for symbol, the C ABI that HOMME's Fortran driver for the
+ * theta-l_kokkos target already binds (bind(c) interfaces), so that driver links against this
+ * library unchanged.  Fortran bind(c) passes scalars and type(c_ptr) BY REFERENCE, hence every
+ * scalar is a pointer and every array argument is a pointer to a pointer.  Arrays are Fortran
+ * ordered (column major), element/time-level indices follow the reference (see each entry).
+ * H/ = components/homme/ in the reference tree.
+ *
+ * The second group (thetal_b200_* and *_c additions) is the finer-grained surface used by the
+ * parity tests and by drivers that keep prim_run_subcycle in Fortran.
+ *
+ * All functions are void like the reference's; fatal conditions print to stderr and abort()
+ * unless thetal_b200_set_abort_on_error(0) was called, in which case the error is latched and
+ * readable with thetal_b200_last_error().
+ */
+#ifndef THETAL_B200_H
+#define THETAL_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef const double *const *thetal_f90ptr;   /* Fortran "type(c_ptr), intent(in)" (by reference) */
+typedef double *const *thetal_f90ptr_out;
+
+/* ---- session / communicator ---------------------------------------------------------------- */
+/* H/src/share/cxx/prim_cxx_driver_base.F90:46-57,125-128; impl Hommexx_Session.cpp:73,97,
+ * mpi/mpi_cxx_f90_interface.cpp:20-28 */
+void initialize_hommexx_session(void);
+void finalize_hommexx_session(void);
+void reset_cxx_comm(const int *f_comm);       /* MPI_Fint handle; ranks come from thetal_b200_init_comm */
+
+/* ---- connectivity: H/src/share/cxx/prim_cxx_driver_base.F90:147-196; impl
+ * mpi/mpi_cxx_f90_interface.cpp:30-85.  All indices 1-based; pos = (dir+1)*max_corner_elems+idx,
+ * dir: W=0,E=1,S=2,N=3,SW=4,SE=5,NW=6,NE=7 (control_mod.F90 west=1..neast=8). */
+void init_connectivity(const int *num_local_elems, const int *max_corner_elems);
+void add_connection(const int *e1_lid, const int *e1_gid, const int *e1_pos, const int *e1_pid,
+                    const int *e2_lid, const int *e2_gid, const int *e2_pos, const int *e2_pid);
+void finalize_connectivity(void);
+
+/* ---- initialisation: H/src/theta-l_kokkos/theta_f2c_mod.F90:10-186; impl
+ * H/src/theta-l_kokkos/cxx/cxx_f90_interface_theta.cpp:41-686 */
+void init_simulation_params_c(const int *remap_alg, const int *limiter_option, const int *rsplit,
+    const int *qsplit, const int *time_step_type, const int *qsize, const int *state_frequency,
+    const double *nu, const double *nu_p, const double *nu_q, const double *nu_s,
+    const double *nu_div, const double *nu_top, const int *hypervis_order,
+    const int *hypervis_subcycle, const int *hypervis_subcycle_tom,
+    const double *hypervis_scaling, const double *laplace_scaling, const double *dcmip16_mu,
+    const int *ftype, const int *theta_adv_form, const int *prescribed_wind,
+    const int *use_moisture, const int *disable_diagnostics, const int *use_cpstar,
+    const int *transport_alg, const int *theta_hydrostatic_mode, const char **test_case,
+    const int *dt_remap_factor, const int *dt_tracer_factor, const double *scale_factor,
+    const double *laplacian_rigid_factor, const int *nsplit, const int *pgrad_correction,
+    const double *dp3d_thresh, const double *vtheta_thresh,
+    const int *internal_diagnostics_level, const int *do_3d_turbulence,
+    const double *tom_sponge_start);
+void init_elements_c(const int *nelemd);
+void init_hvcoord_c(const double *ps0, thetal_f90ptr hyam, thetal_f90ptr hyai,
+                    thetal_f90ptr hybm, thetal_f90ptr hybi);
+void init_time_level_c(const int *nm1, const int *n0, const int *np1, const int *nstep,
+                       const int *nstep0);            /* 1-based time levels */
+void init_reference_element_c(thetal_f90ptr deriv, thetal_f90ptr mass);  /* Dvv(np,np), mp(np,np) */
+/* ie is 0-based here (the Fortran passes ie-1, H/src/theta-l_kokkos/prim_driver_mod.F90:242) */
+void init_elements_2d_c(const int *ie, thetal_f90ptr D, thetal_f90ptr Dinv, thetal_f90ptr fcor,
+    thetal_f90ptr spheremp, thetal_f90ptr rspheremp, thetal_f90ptr metdet, thetal_f90ptr metinv,
+    thetal_f90ptr tensorvisc, thetal_f90ptr vec_sph2cart, const double *sphere_cart_vec,
+    const double *sphere_latlon_vec, thetal_f90ptr tensorvisc2);
+void init_tensorvisc_c(const int *ie, thetal_f90ptr tensorvisc);
+void init_tensorvisc2_c(const int *ie, thetal_f90ptr tensorvisc2);
+void init_geopotential_c(const int *ie, thetal_f90ptr phis, thetal_f90ptr gradphis);
+void init_diagnostics_c(thetal_f90ptr q, thetal_f90ptr qvar, thetal_f90ptr qmass,
+    thetal_f90ptr q1mass, thetal_f90ptr iener, thetal_f90ptr kener, thetal_f90ptr pener);
+/* flat arrays (np,np,[2],nlev|nlevp,timelevels,nelemd), H/src/theta-l_kokkos/element_state.F90:35-67 */
+void init_elements_states_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vtheta_dp,
+    thetal_f90ptr phinh_i, thetal_f90ptr dp3d, thetal_f90ptr qdp, thetal_f90ptr ps_v);
+void init_reference_states_c(thetal_f90ptr theta_ref, thetal_f90ptr dp_ref, thetal_f90ptr phi_ref,
+    thetal_f90ptr nu_scale_top);
+void init_functors_c(const int *allocate_buffer);
+void init_boundary_exchanges_c(void);
+void initialize_dp3d_from_ps_c(void);
+
+/* ---- run time: theta_f2c_mod.F90:189-236; impl H/src/share/cxx/prim_driver.cpp:60-181 */
+void push_forcing_to_c(const double *fm, const double *fvtheta, const double *ft,
+                       const double *fphi, const double *fq);
+void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int *np1,
+                         const int *next_output_step, const int *nsplit_iter);
+void cxx_push_results_to_f90(thetal_f90ptr_out v, thetal_f90ptr_out w_i, thetal_f90ptr_out vtheta_dp,
+    thetal_f90ptr_out phinh_i, thetal_f90ptr_out dp3d, thetal_f90ptr_out ps_v, thetal_f90ptr_out qdp,
+    thetal_f90ptr_out q, thetal_f90ptr_out omega_p);
+void push_test_state_to_c(thetal_f90ptr ps_v, thetal_f90ptr dp3d, thetal_f90ptr vtheta_dp,
+    thetal_f90ptr phinh_i, thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr eta_dot_dpdn,
+    thetal_f90ptr vn0);
+void sync_diagnostics_to_host_c(void);
+
+/* ================= additions (not in the reference ABI) ===================================== */
+/* nlev is a compile-time constant in the reference (dimensions_mod.F90:30-36); here it is set
+ * once before init_elements_c.  np is fixed at 4. */
+void thetal_b200_set_nlev(const int *nlev);
+/* multi-GPU: one rank per GPU.  nccl_id = 128-byte ncclUniqueId from rank 0 (NULL when nranks==1). */
+void thetal_b200_init_comm(const int *rank, const int *nranks, const int *device, const void *nccl_id);
+void thetal_b200_get_nccl_id(void *nccl_id_out);
+void thetal_b200_set_abort_on_error(const int *flag);
+int  thetal_b200_last_error(void);             /* 0 = ok; message via thetal_b200_last_error_msg */
+const char *thetal_b200_last_error_msg(void);
+/* extra controls the reference keeps in Fortran modules: control_mod.F90:101-103, model_init_mod */
+void thetal_b200_set_extra_params(const int *hv_ref_profiles_unused, const int *nlev_tom);
+
+/* the step and its pieces; time levels 0-based, argument order of the Fortran routines:
+ * prim_advance_exp  H/src/theta-l/share/prim_advance_mod.F90:81
+ * compute_andor_apply_rhs(np1,nm1,n0,dt2,...,eta_ave_w,scale1,scale2,scale3)  :1023-1024
+ * compute_stage_value_dirk(nm1,alphadt_nm1,n0,alphadt_n0,np1,dt2,...,itercount,itererr) imex_mod.F90:60-61
+ * advance_hypervis(...,nt,...,dt2,eta_ave_w)  prim_advance_mod.F90:546 */
+void prim_advance_exp_c(const double *dt, const int *nm1, const int *n0, const int *np1,
+                        const int *nstep, const int *compute_diagnostics);
+void caar_c(const int *np1, const int *nm1, const int *n0, const double *dt2,
+            const double *eta_ave_w, const double *scale1, const double *scale2,
+            const double *scale3);
+void dirk_c(const int *nm1, const double *alphadt_nm1, const int *n0, const double *alphadt_n0,
+            const int *np1, const double *dt2, int *itercount, double *itererr);
+void advance_hypervis_c(const int *nt, const double *dt2, const double *eta_ave_w);
+/* host<->device transfers of single pieces (tests, bench e2e) */
+void thetal_b200_get_derived(double *vn0, double *eta_dot_dpdn, double *omega_p);
+void thetal_b200_zero_derived(void);
+void thetal_b200_sync(void);
+/* run `nsteps` dynamics steps back to back (time-level rotation of prim_run_subcycle without
+ * vertical remap); returns elapsed device milliseconds measured with CUDA events */
+double thetal_b200_time_steps(const double *dt, const int *nsteps, int *nm1, int *n0, int *np1);
+/* average per-kernel-family device time (ms) of the last thetal_b200_time_steps call:
+ * out[0]=caar_pre out[1]=dss_post out[2]=dirk out[3]=hypervis(all) out[4]=combine; returns launches */
+long thetal_b200_launch_count(void);
+void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
+                              double *ms_by_family, int nfamily);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
