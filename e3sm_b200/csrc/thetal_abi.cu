@@ -52,6 +52,9 @@ struct Session {
   unsigned long long *d_maxdelta = nullptr;
   bool device_ready = false;
   long launches = 0;
+  bool prof = false;
+  double prof_ms[8] = {0};
+  cudaEvent_t pe0 = nullptr, pe1 = nullptr;
   // DIRK statistics (element_state.F90:20-22)
   int max_itercnt = 0;
   double max_deltaerr = 0;
@@ -428,17 +431,27 @@ void check_device_errors(const char *where)
   }
 }
 
+struct ProfScope {   // per-family device time when thetal_b200_profile_step is active
+  int fam;
+  explicit ProfScope(int f) : fam(f) { if (S.prof) cudaEventRecord(S.pe0, S.stream); }
+  ~ProfScope() {
+    if (!S.prof) return;
+    cudaEventRecord(S.pe1, S.stream); cudaEventSynchronize(S.pe1);
+    float ms = 0; cudaEventElapsedTime(&ms, S.pe0, S.pe1); S.prof_ms[fam] += ms;
+  }
+};
+
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
 void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3)
 {
   CaarArgs a;
   a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
   a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
-  launch_caar_pre(a, S.stream);
+  { ProfScope ps(0); launch_caar_pre(a, S.stream); }
   DssArgs d;
   d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
   d.do_limiter = (s3 != 0.0);
-  launch_caar_dss_post(d, S.stream);
+  { ProfScope ps(1); launch_caar_dss_post(d, S.stream); }
   S.launches += 2;
 }
 
@@ -448,12 +461,13 @@ void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
   a.np1 = S.tl[np1]; a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.geo = S.geo; a.prm = S.prm;
   a.dt2 = dt2; a.alphadt_n0 = a_n0; a.alphadt_nm1 = a_nm1;
   a.err = S.d_err; a.max_iter = S.d_maxiter; a.max_deltaerr_bits = S.d_maxdelta;
-  launch_dirk(a, S.stream);
+  { ProfScope ps(2); launch_dirk(a, S.stream); }
   S.launches += 1;
 }
 
 void run_hypervis(int nt, double dt2, double eta_ave_w)
 {
+  ProfScope ps(3);
   (void)eta_ave_w;   // dpdiss_ave / dpdiss_biharmonic diagnostics (PA:651-656) are not carried
   HvArgs a;
   a.st = S.tl[nt]; a.geo = S.geo; a.ref = S.ref; a.prm = S.prm;
@@ -484,7 +498,7 @@ void run_combo(int kind, int ia, int ib, int ic)
 {
   ComboArgs c;
   c.a = S.tl[ia]; c.b = S.tl[ib]; c.c = S.tl[ic]; c.geo = S.geo; c.prm = S.prm; c.kind = kind;
-  launch_combo(c, S.stream);
+  { ProfScope ps(4); launch_combo(c, S.stream); }
   S.launches += 1;
 }
 
@@ -662,6 +676,10 @@ void thetal_b200_sync(void)
 }
 long thetal_b200_launch_count(void) { return S.launches; }
 
+void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
+                              double *ms_by_family, int nfamily);
+
+
 // ---------------------------------------------------------------- the step
 static bool tl_ok(int t) { return t >= 0 && t < NTL; }
 
@@ -742,3 +760,18 @@ double thetal_b200_time_steps(const double *dt, const int *nsteps, int *nm1, int
 }
 
 }  // extern "C"
+
+namespace { void run_prim_advance_exp(double dt, int nm1, int n0, int np1); }
+extern "C" void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
+                                         double *ms_by_family, int nfamily)
+{
+  require(S.device_ready, "thetal_b200_profile_step before init");
+  if (!S.pe0) { CUDA_OK(cudaEventCreate(&S.pe0)); CUDA_OK(cudaEventCreate(&S.pe1)); }
+  for (double &m : S.prof_ms) m = 0;
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  S.prof = true;
+  run_prim_advance_exp(*dt, *nm1, *n0, *np1);
+  S.prof = false;
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  for (int i = 0; i < nfamily && i < 8; i++) ms_by_family[i] = S.prof_ms[i];
+}

@@ -345,7 +345,7 @@ typedef struct {
 static void ws_alloc(caar_ws *w, int nlev)
 {
   const size_t L = 16*(size_t)(nlev + 1);
-  const int n1 = 29, n2 = 10; /* scalar-sized and vector-sized arrays */
+  const int n1 = 28, n2 = 11; /* scalar-sized and vector-sized arrays */
   w->base = (double *)calloc((n1 + 2*n2)*L, sizeof(double));
   double *q = w->base;
 #define A1(x) w->x = q; q += L

@@ -1,0 +1,162 @@
+"""Pins for the CPU oracle.  The reference holds no golden vectors for this path;
+what it does hold are invariants coded in the Fortran itself, re-run here against the oracle:
+  analytic vs finite-difference DIRK Jacobian   imex_mod.F90:473-574 (tolerance 1e-3 of |J|inf, :565)
+  tridiagonal solver residual <= 1e5*eps         imex_mod.F90:601-642
+  hydrostatic inverse |1-dpnh_dp_i| < 1e-10      element_ops.F90:740-750
+  sphere area = 4 pi                             global_norms_mod.F90:107-228 / geometry_mod.F90:193
+  DSS of a C0 field is the identity              edge_mod / mass_matrix_mod
+  dry-mass conservation of CAAR                  prim_advance_mod.F90:1230-1246 (comment)
+  w boundary condition after the step            prim_advance_mod.F90:1782-1794
+"""
+import ctypes
+import os
+from ctypes import POINTER, byref, c_double, c_int
+
+import numpy as np
+import pytest
+
+from conftest import rel_l2
+from e3sm_b200.geometry import G, KAPPA, dss_numpy
+from e3sm_b200.initial import make_c0
+
+_DP = POINTER(c_double)
+
+
+def P(a):
+    return a.ctypes.data_as(_DP)
+
+
+@pytest.fixture(scope="module")
+def orc(case_c1):
+    from oracle.oracle import Oracle
+    p, grid, hv, st0, phis, gradphis, refs = case_c1
+    st = st0.copy()
+    return Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=os.cpu_count() or 1), st
+
+
+def test_sphere_area(case_c1):
+    grid = case_c1[1]
+    assert abs(grid.sphere_area() - 4 * np.pi) < 1e-12
+    assert grid.nnodes == 6 * grid.ne ** 2 * 9 + 2            # Euler: unique GLL nodes
+
+
+def test_dss_idempotent_on_c0(case_c1):
+    grid = case_c1[1]
+    rng = np.random.default_rng(0)
+    f = make_c0(grid, rng.standard_normal((grid.nelem, 3, 16)))
+    g = make_c0(grid, f)
+    assert rel_l2(g, f) < 1e-14
+    # contributors of a node really are the same physical point
+    src = grid.dss_src
+    e, p, j = np.nonzero(src >= 0)
+    s = src[e, p, j]
+    assert np.abs(grid.cart[e, p] - grid.cart[s // 16, s % 16]).max() < 1e-14
+
+
+def test_hydrostatic_inverse(orc, case_c1):
+    """phi_from_eos is the discrete inverse of pnh_and_exner_from_eos (element_ops.F90:740-750)"""
+    o, st = orc
+    nlev = o.hv.nlev
+    pnh = np.zeros((nlev, 16)); exner = np.zeros((nlev, 16)); mu = np.zeros((nlev + 1, 16))
+    err = c_int(0)
+    for ie in (0, 17, 95):
+        o.lib.orc_eos(byref(o.c), P(st.vtheta_dp[ie, 0]), P(st.dp3d[ie, 0]), P(st.phinh_i[ie, 0]),
+                      P(pnh), P(exner), P(mu), byref(err))
+        assert err.value == 0
+        assert np.abs(1 - mu).max() < 1e-10
+
+
+def test_dirk_jacobian_vs_finite_difference(orc, case_c1):
+    """analytic Jacobian vs FD of the residual, as test_imex_jacobian (imex_mod.F90:473-574)"""
+    o, st = orc
+    nlev = o.hv.nlev
+    ie, dt2 = 5, 100.0
+    th, dp = st.vtheta_dp[ie, 0].copy(), st.dp3d[ie, 0].copy()
+    phi = st.phinh_i[ie, 0].copy()
+    dphi = phi[1:] - phi[:-1]
+    pnh = np.zeros((nlev, 16)); exner = np.zeros((nlev, 16)); mu = np.zeros((nlev + 1, 16))
+    err = c_int(0)
+    o.lib.orc_eos(byref(o.c), P(th), P(dp), P(phi), P(pnh), P(exner), P(mu), byref(err))
+    JL = np.zeros((nlev - 1, 16)); JD = np.zeros((nlev, 16)); JU = np.zeros((nlev - 1, 16))
+    o.lib.orc_dirk_jacobian(byref(o.c), P(JL), P(JD), P(JU), c_double(dt2), P(dp), P(dphi), P(pnh))
+    # FD: F_k(phi) = phi_k-part + (dt2 g)^2 (1 - mu_k); perturb phi_l by eps
+    eps = 1e-4
+    norm = np.abs(JD).max()
+    for l in (0, 1, nlev // 2, nlev - 2, nlev - 1):
+        ph2 = phi.copy(); ph2[l] += eps
+        mu2 = np.zeros_like(mu)
+        o.lib.orc_eos(byref(o.c), P(th), P(dp), P(ph2), P(pnh), P(exner), P(mu2), byref(err))
+        dF = (dt2 * G) ** 2 * (mu[:nlev] - mu2[:nlev]) / eps            # d/dphi_l of (dt g)^2 (1-mu_k)
+        assert np.abs((1 + dF[l]) - JD[l]).max() / norm < 1e-3
+        if l > 0:
+            assert np.abs(dF[l - 1] - JU[l - 1]).max() / norm < 1e-3
+        if l < nlev - 1:
+            assert np.abs(dF[l + 1] - JL[l]).max() / norm < 1e-3
+
+
+def test_tridiag_residual(orc):
+    """solve_strict_diag_dominant_tridiag residual <= 1e5*eps (imex_mod.F90:601-642)"""
+    o, _ = orc
+    nlev = 26
+    rng = np.random.default_rng(3)
+    dl = -rng.uniform(0.1, 1, (nlev - 1, 16)); du = -rng.uniform(0.1, 1, (nlev - 1, 16))
+    d = np.ones((nlev, 16)); d[:-1] -= du; d[1:] -= dl
+    x_true = rng.standard_normal((nlev, 16))
+    b = d * x_true
+    b[:-1] += du * x_true[1:]
+    b[1:] += dl * x_true[:-1]
+    dd, x = d.copy(), b.copy()
+    o.lib.orc_tridiag(c_int(nlev), P(dl), P(dd), P(du), P(x))
+    assert np.abs(x - x_true).max() / np.abs(x_true).max() < 1e5 * np.finfo(float).eps
+
+
+def test_caar_conserves_dry_mass_and_wbc(case_c1, parity_state_c1):
+    from oracle.oracle import Oracle
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    st = parity_state_c1.copy()
+    o = Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=os.cpu_count() or 1)
+    o.compute_andor_apply_rhs(2, 1, 1, 100.0, 0.0, 1.0, 0.0, 1.0)
+    w = grid.spheremp                                          # global integral = sum_e sum_p spheremp f
+    m0 = np.sum(st.dp3d[:, 1].sum(axis=1) * w)
+    m1 = np.sum(st.dp3d[:, 2].sum(axis=1) * w)
+    assert abs(m1 - m0) / m0 < 1e-13
+    nlev = hv.nlev
+    wb = (st.v[:, 2, nlev - 1, 0] * gradphis[:, 0] + st.v[:, 2, nlev - 1, 1] * gradphis[:, 1]) / G
+    assert np.abs(wb - st.w_i[:, 2, nlev]).max() < 1e-10       # prim_advance_mod.F90:1787
+    # result is C0
+    for f in st.FIELDS:
+        a = getattr(st, f)[:, 2]
+        assert rel_l2(make_c0(grid, a), a) < 1e-13, f
+
+
+def test_step_is_stable_and_converges(case_c1):
+    """30 steps of JW at dt=600 on ne4: Newton converges in a few iterations, state stays physical"""
+    from oracle.oracle import Oracle
+    p, grid, hv, st0, phis, gradphis, refs = case_c1
+    st = st0.copy()
+    o = Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=os.cpu_count() or 1)
+    nm1, n0, np1 = 0, 1, 2
+    for _ in range(30):
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        nm1, n0, np1 = n0, np1, nm1
+    assert o.error_flag == 0 and o.c.max_itercnt <= 6 and o.c.max_deltaerr < 1e-11
+    assert np.isfinite(st.v).all() and (st.dp3d > 0).all()
+    assert np.abs(st.v[:, n0]).max() < 60.0
+    ps = hv.hyai[0] * hv.ps0 + st.dp3d[:, n0].sum(axis=1)
+    assert 9.8e4 < ps.min() and ps.max() < 1.02e5
+
+
+@pytest.mark.parametrize("tt", [5, 7, 9, 10])
+def test_oracle_time_level_aliasing(case_c1, parity_state_c1, tt):
+    """prim_advance_exp must not depend on which physical slots hold nm1/n0/np1"""
+    from oracle.oracle import Oracle
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    p = p.with_(tstep_type=tt)
+    dt = p.tstep if tt != 5 else 0.5   # explicit NH: vertical acoustic CFL
+    a = parity_state_c1.copy(); b = parity_state_c1.copy()
+    oa = Oracle(grid, hv, p, phis, gradphis, refs, a, nthreads=2)
+    ob = Oracle(grid, hv, p, phis, gradphis, refs, b, nthreads=1)
+    oa.prim_advance_exp(dt, 0, 1, 2)
+    ob.prim_advance_exp(dt, 2, 0, 1)
+    for f in a.FIELDS:
+        assert np.array_equal(getattr(a, f)[:, 2], getattr(b, f)[:, 1]), f   # also thread-count independent
