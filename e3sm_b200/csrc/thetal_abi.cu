@@ -775,3 +775,41 @@ extern "C" void thetal_b200_profile_step(const double *dt, const int *nm1, const
   CUDA_OK(cudaStreamSynchronize(S.stream));
   for (int i = 0; i < nfamily && i < 8; i++) ms_by_family[i] = S.prof_ms[i];
 }
+
+// ---- single-time-level transfers (bench e2e; a driver that only needs the new state) ----------
+extern "C" void thetal_b200_push_level(const int *tl, const double *v, const double *w_i, const double *vtheta_dp,
+                                       const double *phinh_i, const double *dp3d)
+{ // host arrays [ie][k][(c)][16] of ONE time level -> device, asynchronous on the library stream
+  require(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_push_level");
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  const StatePtrs &d = S.tl[*tl];
+  CUDA_OK(cudaMemcpyAsync(d.v, v, n * 32 * nlev * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaMemcpyAsync(d.w, w_i, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaMemcpyAsync(d.th, vtheta_dp, n * 16 * nlev * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaMemcpyAsync(d.phi, phinh_i, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaMemcpyAsync(d.dp, dp3d, n * 16 * nlev * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+}
+extern "C" void thetal_b200_pull_level(const int *tl, double *v, double *w_i, double *vtheta_dp,
+                                       double *phinh_i, double *dp3d)
+{
+  require(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_pull_level");
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  const StatePtrs &d = S.tl[*tl];
+  CUDA_OK(cudaMemcpyAsync(v, d.v, n * 32 * nlev * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaMemcpyAsync(w_i, d.w, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaMemcpyAsync(vtheta_dp, d.th, n * 16 * nlev * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaMemcpyAsync(phinh_i, d.phi, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaMemcpyAsync(dp3d, d.dp, n * 16 * nlev * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+}
+extern "C" void thetal_b200_pin_host(void *ptr, const long *bytes, const int *pin)
+{
+  if (*pin) CUDA_OK(cudaHostRegister(ptr, (size_t)*bytes, cudaHostRegisterDefault));
+  else CUDA_OK(cudaHostUnregister(ptr));
+}
+// enqueue one dynamics step without synchronising (bench e2e)
+extern "C" void thetal_b200_enqueue_step(const double *dt, const int *nm1, const int *n0, const int *np1)
+{
+  require(S.device_ready, "thetal_b200_enqueue_step before init");
+  run_prim_advance_exp(*dt, *nm1, *n0, *np1);
+}

@@ -131,6 +131,16 @@ long thetal_b200_launch_count(void);
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);
 
+/* single-time-level transfers: host arrays [ie][k][(c)][16] of ONE time level (0-based tl),
+ * asynchronous H2D on the library stream; pull synchronises.  Used by the bench's e2e leg and by
+ * drivers that only need the new state (the reference pulls all three levels). */
+void thetal_b200_push_level(const int *tl, const double *v, const double *w_i, const double *vtheta_dp,
+                            const double *phinh_i, const double *dp3d);
+void thetal_b200_pull_level(const int *tl, double *v, double *w_i, double *vtheta_dp,
+                            double *phinh_i, double *dp3d);
+void thetal_b200_pin_host(void *ptr, const long *bytes, const int *pin);   /* cudaHostRegister */
+void thetal_b200_enqueue_step(const double *dt, const int *nm1, const int *n0, const int *np1);
+
 #ifdef __cplusplus
 }
 #endif
