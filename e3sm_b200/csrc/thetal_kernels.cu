@@ -458,11 +458,11 @@ void launch_caar_dss_post(const DssArgs &A, cudaStream_t st)
 // ==========================================================================================
 
 constexpr int DIRK_THREADS = 256;
-constexpr int DIRK_ARRAYS = 12;
+constexpr int DIRK_ARRAYS = 6;
 
 __host__ __device__ inline size_t dirk_smem_bytes(int nlev)
 {
-  return sizeof(double) * 16 * ((size_t)DIRK_ARRAYS * nlev + 2) + 64 * sizeof(double);
+  return sizeof(double) * (16 * ((size_t)DIRK_ARRAYS * nlev + 1) + 64);
 }
 
 __device__ __forceinline__ double block_max(double v, double *red, int tid)
@@ -486,34 +486,54 @@ __device__ __forceinline__ double gwphis_at(const double *v, const double *dp, i
   return (vi1 * g1 + vi2 * g2) * c_hybi[k];
 }
 
-__global__ void __launch_bounds__(DIRK_THREADS) dirk_kernel(const DirkArgs A)
+// Layout of the solve: thread tid owns the point-levels q = tid + j*256 (j < ITEMS) of the element
+// for the whole kernel, so everything only its owner touches (Rgas*vtheta_dp, the stage right-hand
+// sides w0 and dphi0) stays in registers; only what a vertical neighbour or the tridiagonal sweep
+// reads lives in shared memory (6 tiles per level: 1/dp_i, w, pnh, pnh/dphi, x, dphi).  That is
+// 55 KB per element at L72, so three to four elements are resident per SM and the serial sweeps of
+// one element overlap the pow-heavy parallel phases of the others.
+// Deviations from the Fortran operation order (all far below the 1e-10 parity budget):
+//  * (pnh_k - pnh_{k-1}) is multiplied by a stored 1/dp_i instead of divided by dp_i (<= 1 ulp of mu);
+//  * the tridiagonal solve multiplies by reciprocals of the pivots (the solve only steers Newton);
+//  * the EOS after the last Newton update is skipped (its result is never used, IM:324-336).
+template <int ITEMS>
+__global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : 3)) dirk_kernel(const DirkArgs A)
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
-  const int ie = blockIdx.x, tid = threadIdx.x, n16 = 16 * nlev;
-  double *sdp = smem, *sth = sdp + n16, *sdphi0 = sth + n16, *sw0 = sdphi0 + n16, *sphi0 = sw0 + n16;
-  double *sw = sphi0 + n16 + 16;           // phi0 has nlevp tiles (bottom = phis)
-  double *sdphi = sw + n16, *spnh = sdphi + n16, *sx = spnh + n16, *sb = sx + n16, *sc = sb + n16;
-  double *sD = sc + n16;                   // modified diagonal / reciprocal
-  double *red = sD + n16 + 16;
+  const int ie = blockIdx.x, tid = threadIdx.x, n16 = 16 * nlev, p = tid & 15;
+  double *srdpi = smem, *sw = srdpi + n16, *spnh = sw + n16, *sc = spnh + n16, *sr = sc + n16;
+  double *sx = sr + n16;                   // nlevp tiles (phi0 incl. phis during set-up)
+  double *red = sx + n16 + 16;
   const double g = G_GRAV, dt2 = A.dt2;
   const double ptop = A.prm.ptop;
 
   const double *gth = A.np1.th + (size_t)ie * n16, *gdp = A.np1.dp + (size_t)ie * n16;
   const double *gv = A.np1.v + (size_t)ie * 2 * n16;
   double *gw = A.np1.w + (size_t)ie * 16 * nlevp, *gphi = A.np1.phi + (size_t)ie * 16 * nlevp;
-  const double gp1 = A.geo.gradphis[(size_t)ie * 32 + (tid & 15)], gp2 = A.geo.gradphis[(size_t)ie * 32 + 16 + (tid & 15)];
+  const double gp1 = A.geo.gradphis[(size_t)ie * 32 + p], gp2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
   int bad = 0;
+  double rth[ITEMS], w0[ITEMS], dphi0[ITEMS], phi0[ITEMS];
 
   // ---- load, wmax (IM:168-170) ----
   double wmax = 0.0;
-  for (int q = tid; q < n16; q += DIRK_THREADS) {
-    sdp[q] = gdp[q]; sth[q] = gth[q];
-    const double w = gw[q];
-    sw0[q] = w; sphi0[q] = gphi[q];
-    wmax = fmax(wmax, fabs(w));
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const int q = tid + j * DIRK_THREADS;
+    rth[j] = 0; w0[j] = 0; dphi0[j] = 0; phi0[j] = 0;
+    if (q < n16) {
+      const double dp = gdp[q], th = gth[q];
+      const double dpi = (q >= 16) ? (dp + gdp[q - 16]) / 2 : dp;
+      srdpi[q] = 1.0 / dpi;
+      sc[q] = dp;                           // temporary: pressure scan below
+      if (th < 0 || dp < 0) bad = 1;
+      rth[j] = RGAS * th;
+      const double w = gw[q];
+      w0[j] = w; phi0[j] = gphi[q];
+      wmax = fmax(wmax, fabs(w));
+    }
   }
-  if (tid < 16) { sphi0[n16 + tid] = gphi[n16 + tid]; wmax = fmax(wmax, fabs(gw[n16 + tid])); }
+  if (tid < 16) wmax = fmax(wmax, fabs(gw[n16 + tid]));
   wmax = fmax(1.0, block_max(wmax, red, tid));
 
   // ---- explicit stiff terms of earlier stages (IM:176-205) ----
@@ -530,64 +550,83 @@ __global__ void __launch_bounds__(DIRK_THREADS) dirk_kernel(const DirkArgs A)
       spnh[q] = eos_pnh(RGAS * th / (-dphi));
     }
     __syncthreads();
-    for (int q = tid; q < n16; q += DIRK_THREADS) {
-      const int k = q >> 4, p = q & 15;
-      double mu;
-      if (k == 0) mu = 2 * (spnh[q] - ptop) / tdp[q];
-      else mu = (spnh[q] - spnh[q - 16]) / ((tdp[q] + tdp[q - 16]) / 2);
-      sw0[q] = sw0[q] + dt3 * g * (mu - 1);
-      const double gwh = (k == 0) ? 0.0 : gwphis_at(tv, tdp, k, p, gp1, gp2);
-      sphi0[q] = sphi0[q] + dt3 * g * tw[q] - dt3 * gwh;
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+      const int q = tid + j * DIRK_THREADS;
+      if (q < n16) {
+        const int k = q >> 4;
+        double mu;
+        if (k == 0) mu = 2 * (spnh[q] - ptop) / tdp[q];
+        else mu = (spnh[q] - spnh[q - 16]) / ((tdp[q] + tdp[q - 16]) / 2);
+        w0[j] = w0[j] + dt3 * g * (mu - 1);
+        const double gwh = (k == 0) ? 0.0 : gwphis_at(tv, tdp, k, p, gp1, gp2);
+        phi0[j] = phi0[j] + dt3 * g * tw[q] - dt3 * gwh;
+      }
     }
     __syncthreads();
   }
-  // ---- wphis(np1) term (IM:208-211), Jacobian coefficient b (IM:416,422,430) ----
-  {
-    const double a = (dt2 * g) * (dt2 * g) / (1 - KAPPA);
-    for (int q = tid; q < n16; q += DIRK_THREADS) {
-      const int k = q >> 4, p = q & 15;
+  // ---- wphis(np1) term (IM:208-211); phi0 goes to global (it is the base of the final update) ----
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const int q = tid + j * DIRK_THREADS;
+    if (q < n16) {
+      const int k = q >> 4;
       const double gwh = (k == 0) ? 0.0 : gwphis_at(gv, gdp, k, p, gp1, gp2);
-      sphi0[q] = sphi0[q] - dt2 * gwh;
-      sb[q] = (k == 0) ? a / sdp[q] : 2 * a / (sdp[q - 16] + sdp[q]);
+      phi0[j] = phi0[j] - dt2 * gwh;
+      sx[q] = phi0[j];
+      gphi[q] = phi0[j];
     }
   }
+  if (tid < 16) sx[n16 + tid] = gphi[n16 + tid];
   __syncthreads();
   // ---- hydrostatic initial guess phi_from_eos (EOS:286-302, IM:228-230) ----
-  // sx <- Rgas*vtheta_dp*(p/p0)^(kappa-1)/p0 needs the pressure scan first
   if (tid < 16) {
     double p_i = ptop;
-    for (int k = 0; k < nlev; k++) { const double pn = p_i + sdp[k * 16 + tid]; sc[k * 16 + tid] = (pn + p_i) / 2; p_i = pn; }
+    for (int k = 0; k < nlev; k++) { const double pn = p_i + sc[k * 16 + tid]; spnh[k * 16 + tid] = (pn + p_i) / 2; p_i = pn; }
   }
   __syncthreads();
-  for (int q = tid; q < n16; q += DIRK_THREADS)
-    sx[q] = (RGAS * sth[q] * pow(sc[q] / P0, KAPPA - 1)) / P0;
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const int q = tid + j * DIRK_THREADS;
+    if (q < n16) sr[q] = (rth[j] * pow(spnh[q] / P0, KAPPA - 1)) / P0;
+  }
   __syncthreads();
-  if (tid < 16) {   // sD <- phi_np1 (hydrostatic), bottom-up
-    double ph = sphi0[n16 + tid];
-    for (int k = nlev - 1; k >= 0; k--) { ph = ph + sx[k * 16 + tid]; sD[k * 16 + tid] = ph; }
+  if (tid < 16) {   // sr <- phi_np1 (hydrostatic), bottom-up
+    double ph = sx[n16 + tid];
+    for (int k = nlev - 1; k >= 0; k--) { ph = ph + sr[k * 16 + tid]; sr[k * 16 + tid] = ph; }
   }
   __syncthreads();
   int nsafe = 0;
-  for (int q = tid; q < n16; q += DIRK_THREADS) {                                   // IM:234-253
-    const double below = (q + 16 < n16) ? sD[q + 16] : sphi0[q + 16];
-    double dphi = below - sD[q];
-    sdphi0[q] = sphi0[q + 16] - sphi0[q];
-    if (dphi > -g) { dphi = -g; nsafe = 1; }
-    sdphi[q] = dphi;
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {                                                 // IM:234-253
+    const int q = tid + j * DIRK_THREADS;
+    if (q < n16) {
+      const double below = (q + 16 < n16) ? sr[q + 16] : sx[q + 16];
+      double dphi = below - sr[q];
+      dphi0[j] = sx[q + 16] - sx[q];
+      if (dphi > -g) { dphi = -g; nsafe = 1; }
+      spnh[q] = dphi;                       // temporary
+    }
   }
   nsafe = __syncthreads_or(nsafe);
   if (nsafe) {                                                                      // IM:254-260
     if (tid < 16) {
-      double ph = sphi0[n16 + tid];
-      for (int k = nlev - 1; k >= 0; k--) { ph = ph - sdphi[k * 16 + tid]; sD[k * 16 + tid] = ph; }
+      double ph = sx[n16 + tid];
+      for (int k = nlev - 1; k >= 0; k--) { ph = ph - spnh[k * 16 + tid]; sr[k * 16 + tid] = ph; }
     }
     __syncthreads();
   }
-  for (int q = tid; q < n16; q += DIRK_THREADS) {
-    sw[q] = (sD[q] - sphi0[q]) / (dt2 * g);
-    const double th = sth[q], dp = sdp[q], dphi = sdphi[q];
-    if (th < 0 || dp < 0 || dphi > 0) bad = 1;
-    spnh[q] = eos_pnh(RGAS * th / (-dphi));                                         // IM:261
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const int q = tid + j * DIRK_THREADS;
+    if (q < n16) {
+      sw[q] = (sr[q] - sx[q]) / (dt2 * g);
+      const double dphi = spnh[q];
+      if (dphi > 0) bad = 1;
+      const double pnh = eos_pnh(rth[j] / (-dphi));                                 // IM:261
+      spnh[q] = pnh;
+      sc[q] = pnh / dphi;
+    }
   }
   __syncthreads();
 
@@ -595,103 +634,145 @@ __global__ void __launch_bounds__(DIRK_THREADS) dirk_kernel(const DirkArgs A)
   int itercount = 0;
   double deltaerr = 0.0;
   const int maxiter = 20;
+  const double ajac = (dt2 * g) * (dt2 * g) / (1 - KAPPA);                          // IM:414
+  unsigned long long *amin = (unsigned long long *)(red + 32);
+  int *cflag = (int *)(red + 48);
   while (itercount < maxiter) {
-    // residual Fn (IM:263-264 / 326), x = -Fn, c = pnh/dphi
-    for (int q = tid; q < n16; q += DIRK_THREADS) {
-      const int k = q >> 4;
-      double mu;
-      if (k == 0) mu = 2 * (spnh[q] - ptop) / sdp[q];
-      else mu = (spnh[q] - spnh[q - 16]) / ((sdp[q] + sdp[q - 16]) / 2);
-      const double Fn = sw[q] - (sw0[q] + g * dt2 * (mu - 1));
-      sx[q] = -Fn;
-      sc[q] = spnh[q] / sdphi[q];
+    // residual Fn (IM:263-264 / 326), x = -Fn
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+      const int q = tid + j * DIRK_THREADS;
+      if (q < n16) {
+        double mu;
+        if (q < 16) mu = 2 * (spnh[q] - ptop) * srdpi[q];
+        else mu = (spnh[q] - spnh[q - 16]) * srdpi[q];
+        const double Fn = sw[q] - (w0[j] + g * dt2 * (mu - 1));
+        sx[q] = -Fn;
+      }
     }
     __syncthreads();
-    // tridiagonal solve (IM:414-433 assembled on the fly, IM:590-598)
+    // tridiagonal solve J x = -Fn: Jacobian rows (IM:414-433) assembled on the fly from c = pnh/dphi
+    // and b = a/dp_i; Thomas sweeps (IM:590-598) with reciprocal pivots, one column per lane.
     if (tid < 16) {
-      const int p = tid;
-      double U = 2 * sb[p] * sc[p];
-      double D = 1 - U;
-      double x = sx[p];
-      sD[p] = D;
-      for (int k = 0; k < nlev - 1; k++) {
-        const int q1 = (k + 1) * 16 + p;
-        const double b1 = sb[q1];
-        const double L = b1 * sc[q1 - 16];
-        const double U1 = b1 * sc[q1];
-        const double D1raw = (k + 1 < nlev - 1) ? (1 - L - U1) : (1 - L - U1);
-        const double dlk = L / D;
-        D = D1raw - dlk * U;
-        x = sx[q1] - dlk * x;
-        sx[q1] = x;
-        sD[q1] = D;
-        U = U1;
+      double cprev = sc[p];
+      double Uprev = 2 * (ajac * srdpi[p]) * cprev;
+      double r = 1.0 / (1 - Uprev);
+      double y = sx[p];
+      sx[p] = y * r; sc[p] = Uprev * r;
+      double cn = sc[16 + p], bn = ajac * srdpi[16 + p], rn = sx[16 + p];
+      for (int k = 1; k < nlev; k++) {
+        const int q = k * 16 + p;
+        const double c = cn, b = bn, rhs = rn;
+        if (k + 1 < nlev) { cn = sc[q + 16]; bn = ajac * srdpi[q + 16]; rn = sx[q + 16]; }
+        const double L = b * cprev, U = b * c;
+        const double diag = 1 - L - U;
+        const double LU = L * Uprev;
+        const double lr = L * r;
+        const double D = fma(-LU, r, diag);
+        y = fma(-lr, y, rhs);
+        r = 1.0 / D;
+        sx[q] = y * r; sc[q] = U * r;
+        Uprev = U; cprev = c;
       }
-      x = x / D;
-      sx[(nlev - 1) * 16 + p] = x;
+      double x = sx[(nlev - 1) * 16 + p];
+      double un = sc[(nlev - 2) * 16 + p], yn = sx[(nlev - 2) * 16 + p];
       for (int k = nlev - 2; k >= 0; k--) {
         const int q = k * 16 + p;
-        const double Uk = (k == 0) ? 2 * sb[q] * sc[q] : sb[q] * sc[q];
-        x = (sx[q] - Uk * x) / sD[q];
+        const double u = un, yy = yn;
+        if (k > 0) { un = sc[q - 16]; yn = sx[q - 16]; }
+        x = fma(-u, x, yy);
         sx[q] = x;
       }
     }
     __syncthreads();
     // dphi update (IM:278-283) and positivity check
     int anypos = 0;
-    for (int q = tid; q < n16; q += DIRK_THREADS) {
-      double dphi;
-      if (q + 16 < n16) dphi = sdphi0[q] + dt2 * g * ((sw[q + 16] - sw[q]) + (sx[q + 16] - sx[q]));
-      else dphi = sdphi0[q] - dt2 * g * (sw[q] + sx[q]);
-      sdphi[q] = dphi;
-      if (dphi >= 0) anypos = 1;
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+      const int q = tid + j * DIRK_THREADS;
+      if (q < n16) {
+        double dphi;
+        if (q + 16 < n16) dphi = dphi0[j] + dt2 * g * ((sw[q + 16] - sw[q]) + (sx[q + 16] - sx[q]));
+        else dphi = dphi0[j] - dt2 * g * (sw[q] + sx[q]);
+        sr[q] = dphi;
+        if (dphi >= 0) anypos = 1;
+      }
     }
     anypos = __syncthreads_or(anypos);
+    double alpha = 1.0;
     if (anypos) {                                                                   // IM:285-319 (rare)
       if (tid < 16) {
-        const int p = tid;
         int colpos = 0;
-        for (int k = 0; k < nlev; k++) if (sdphi[k * 16 + p] >= 0) colpos = 1;
-        double alpha = 1.0;
-        if (colpos) {
-          for (int k = 0; k < nlev; k++) {
+        for (int k = 0; k < nlev; k++) if (sr[k * 16 + tid] >= 0) colpos = 1;
+        cflag[tid] = colpos;
+        amin[tid] = (unsigned long long)__double_as_longlong(1.0);
+      }
+      __syncthreads();
+      if (cflag[p]) {
+#pragma unroll
+        for (int j = 0; j < ITEMS; j++) {
+          const int q = tid + j * DIRK_THREADS;
+          if (q < n16) {
             double dx, dw;
-            if (k < nlev - 1) { dx = sx[(k + 1) * 16 + p] - sx[k * 16 + p]; dw = sw[(k + 1) * 16 + p] - sw[k * 16 + p]; }
-            else { dx = -sx[k * 16 + p]; dw = -sw[k * 16 + p]; }
+            if (q + 16 < n16) { dx = sx[q + 16] - sx[q]; dw = sw[q + 16] - sw[q]; }
+            else { dx = -sx[q]; dw = -sw[q]; }
             if (dx != 0) {
-              const double alpha_k = -(sdphi0[k * 16 + p] + dt2 * g * dw) / (dt2 * g * dx);
-              if (alpha_k >= 0) alpha = fmin(alpha, alpha_k);
+              const double alpha_k = -(dphi0[j] + dt2 * g * dw) / (dt2 * g * dx);
+              if (alpha_k >= 0) atomicMin(&amin[p], (unsigned long long)__double_as_longlong(fabs(alpha_k)));
             }
           }
-          alpha = alpha / 2;
-          for (int k = 0; k < nlev - 1; k++)
-            sdphi[k * 16 + p] = sdphi0[k * 16 + p] + dt2 * g * ((sw[(k + 1) * 16 + p] - sw[k * 16 + p]) + alpha * (sx[(k + 1) * 16 + p] - sx[k * 16 + p]));
-          sdphi[(nlev - 1) * 16 + p] = sdphi0[(nlev - 1) * 16 + p] - dt2 * g * (sw[(nlev - 1) * 16 + p] + alpha * sx[(nlev - 1) * 16 + p]);
         }
-        red[32 + p] = alpha;
+      }
+      __syncthreads();
+      if (cflag[p]) {
+        alpha = __longlong_as_double((long long)amin[p]) / 2;
+#pragma unroll
+        for (int j = 0; j < ITEMS; j++) {
+          const int q = tid + j * DIRK_THREADS;
+          if (q < n16) {
+            if (q + 16 < n16) sr[q] = dphi0[j] + dt2 * g * ((sw[q + 16] - sw[q]) + alpha * (sx[q + 16] - sx[q]));
+            else sr[q] = dphi0[j] - dt2 * g * (sw[q] + alpha * sx[q]);
+          }
+        }
       }
       __syncthreads();
     }
     double xmax = 0.0;
-    for (int q = tid; q < n16; q += DIRK_THREADS) {
-      const double x = sx[q];
-      const double alpha = anypos ? red[32 + (q & 15)] : 1.0;
-      sw[q] = sw[q] + alpha * x;                                                    // IM:320-322
-      xmax = fmax(xmax, fabs(x));
-      const double th = sth[q], dp = sdp[q], dphi = sdphi[q];
-      if (th < 0 || dp < 0 || dphi > 0) bad = 1;
-      spnh[q] = eos_pnh(RGAS * th / (-dphi));                                       // IM:324
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+      const int q = tid + j * DIRK_THREADS;
+      if (q < n16) {
+        const double x = sx[q];
+        sw[q] = sw[q] + alpha * x;                                                  // IM:320-322
+        xmax = fmax(xmax, fabs(x));
+      }
     }
-    xmax = block_max(xmax, red, tid);   // contains the barriers that publish sw/spnh
+    xmax = block_max(xmax, red, tid);
     deltaerr = xmax / wmax;                                                         // IM:330
     itercount++;
     if (deltaerr < 1.0e-11) break;                                                  // IM:335
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+      const int q = tid + j * DIRK_THREADS;
+      if (q < n16) {
+        const double dphi = sr[q];
+        if (dphi > 0) bad = 1;
+        const double pnh = eos_pnh(rth[j] / (-dphi));                               // IM:324
+        spnh[q] = pnh;
+        sc[q] = pnh / dphi;
+      }
+    }
+    __syncthreads();
   }
   // ---- phi update (IM:339) and write back ----
-  for (int q = tid; q < n16; q += DIRK_THREADS) {
-    const double w = sw[q];
-    gw[q] = w;
-    gphi[q] = sphi0[q] + dt2 * g * w;
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const int q = tid + j * DIRK_THREADS;
+    if (q < n16) {
+      const double w = sw[q];
+      gw[q] = w;
+      gphi[q] = gphi[q] + dt2 * g * w;      // gphi holds phi0 since the set-up phase
+    }
   }
   if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
   if (tid == 0) {
@@ -701,15 +782,26 @@ __global__ void __launch_bounds__(DIRK_THREADS) dirk_kernel(const DirkArgs A)
   }
 }
 
+template <int ITEMS>
+static void launch_dirk_t(const DirkArgs &A, cudaStream_t st, size_t sm)
+{
+  static size_t configured = 0;
+  if (sm > configured) {
+    cudaFuncSetAttribute(dirk_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    configured = sm;
+  }
+  dirk_kernel<ITEMS><<<A.prm.nelem, DIRK_THREADS, sm, st>>>(A);
+}
+
 void launch_dirk(const DirkArgs &A, cudaStream_t st)
 {
   const size_t sm = dirk_smem_bytes(A.prm.nlev);
-  static size_t configured = 0;
-  if (sm > configured) {
-    cudaFuncSetAttribute(dirk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    configured = sm;
-  }
-  dirk_kernel<<<A.prm.nelem, DIRK_THREADS, sm, st>>>(A);
+  const int need = (16 * A.prm.nlev + DIRK_THREADS - 1) / DIRK_THREADS;
+  if (need <= 2) launch_dirk_t<2>(A, st, sm);
+  else if (need <= 4) launch_dirk_t<4>(A, st, sm);
+  else if (need == 5) launch_dirk_t<5>(A, st, sm);
+  else if (need == 6) launch_dirk_t<6>(A, st, sm);
+  else launch_dirk_t<8>(A, st, sm);
 }
 
 // ==========================================================================================
