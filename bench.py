@@ -166,14 +166,20 @@ def run_reference(args, world, rank, td):
 
 def run_ours(args, world, rank, local, td):
     import ctypes
-    from e3sm_b200.dycore import ThetaLDycore, build_case, _ci, _cd
+    from e3sm_b200.dycore import ThetaLDycore, broadcast_nccl_id, build_case, _ci, _cd
     from e3sm_b200.initial import State
+    from e3sm_b200.partition import Partition
     p = config(args.config)
-    grid, hv, st, phis, gradphis, refs = build_case(p)
-    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs, device=local)
+    part, nccl_id = None, None
+    if world > 1:   # elements cut along HOMME's space-filling curve, one slice per GPU, DSS halos over NCCL
+        part = Partition(p.ne, world)
+        nccl_id = broadcast_nccl_id(td, rank)
+    grid, hv, st, phis, gradphis, refs = build_case(p, part=part, rank=rank)
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs, device=local, rank=rank, part=part, nccl_id=nccl_id)
     d.set_state(st)
     L = d.L
-    nelem, nlev = grid.nelem, hv.nlev
+    nelem, nlev = d.nelem, hv.nlev          # elements on this GPU
+    nelem_total = grid.nelem
     K, W = args.steps, max(args.warmup, 3)
     # ---- device-resident timing ----
     ms_w, nm1, n0, np1 = d.time_steps(p.tstep, W, 0, 1, 2)
@@ -186,7 +192,7 @@ def run_ours(args, world, rank, local, td):
     clocks = sampler.stop()
     launches = d.launch_count() - l0
     ms = all_max(td, ms)
-    value = world * nelem * K / (ms * 1e-3)
+    value = nelem_total * K / (ms * 1e-3)
     # ---- per-kernel-family times of one step (CUDA events on the library stream) ----
     fam = (ctypes.c_double * 8)()
     reps = 3
@@ -196,7 +202,7 @@ def run_ours(args, world, rank, local, td):
         acc += np.array(list(fam))
         nm1, n0, np1 = n0, np1, nm1
     acc /= reps
-    names = ["caar_pre", "caar_dss_post", "dirk", "hypervis", "combine"]
+    names = ["caar_pre", "caar_dss_post", "dirk", "hypervis", "combine", "caar_halo"]
     fam_ms = {n: float(acc[i]) for i, n in enumerate(names)}
     peak, peak_kind = measured_peak()
     S = 128 * (6 * nlev + 2)
@@ -212,7 +218,7 @@ def run_ours(args, world, rank, local, td):
     roofline = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": None, "peak_kind": peak_kind,
                 "alg_bytes_per_launch": nelem * alg[dom], "launch_ms": dom_ms}
-    step_gbs = nelem * bstep / (ms / K * 1e-3) / 1e9
+    step_gbs = nelem_total * bstep / (ms / K * 1e-3) / 1e9
     # ---- end to end through the C ABI with host buffers ----
     hst = State(nelem, nlev)
     d.get_state(hst)
@@ -243,8 +249,9 @@ def run_ours(args, world, rank, local, td):
     L.thetal_b200_sync()
     e2e_s = all_max(td, time.perf_counter() - t0)
     d._check()
-    e2e_val = world * nelem * Ke / e2e_s
-    level_bytes = nelem * S
+    e2e_val = nelem_total * Ke / e2e_s
+    level_bytes = nelem_total * S
+    n_exch, halo_bytes = d.halo_stats()
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, cores, sample, _ = cpu_reference_sample(p)
@@ -252,15 +259,18 @@ def run_ours(args, world, rank, local, td):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
+            "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.config}: theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem} elements"
-                                   f"{' per GPU (independent replicas)' if world > 1 else ''}, tstep_type {p.tstep_type}, "
-                                   f"dt={p.tstep:g}s, hypervis_subcycle {p.hypervis_subcycle}, sponge on",
+            "config": {"workload": f"{args.config}: theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem_total} elements"
+                                   f", tstep_type {p.tstep_type}, dt={p.tstep:g}s, hypervis_subcycle {p.hypervis_subcycle}, sponge on",
                        "l2": "inputs larger than L2 (every kernel streams >= 300 MB of state; L2 is 126 MB)",
-                       "parallelism": "1 rank per GPU" + ("" if world == 1 else ", replicas only (no halo exchange yet)")},
-            "sypd": p.tstep * (value / world / nelem) / 365.0,
-            "hbm_gbs_step": step_gbs, "hbm_frac_step": step_gbs / peak, "alg_bytes_per_element_step": bstep,
+                       "parallelism": "1 rank per GPU" + ("" if world == 1 else
+                                      f", HOMME space-filling-curve partition into {world} slices ({nelem} elements on rank 0), "
+                                      f"DSS halos by ncclSend/ncclRecv: {n_exch} exchanges, {halo_bytes / max(n_exch, 1) / 1e6:.2f} MB "
+                                      "sent+received per exchange on rank 0")},
+            "sypd": p.tstep * (value / nelem_total) / 365.0,
+            "hbm_gbs_step": step_gbs, "hbm_frac_step": step_gbs / (peak * world), "alg_bytes_per_element_step": bstep,
             "kernel_ms_per_step": fam_ms,
             "roofline": roofline,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": level_bytes, "d2h_bytes_per_step": level_bytes,
@@ -279,10 +289,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="C2")
+    ap.add_argument("--config", default=None, help="C1..C5; default C2 on 1 GPU, C3 (ne120, partitioned) on N>1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     world, rank, local, td = dist_setup(args.gpus)
+    if args.config is None:
+        args.config = "C2" if world == 1 else "C3"
     if args.impl == "reference":
         if args.steps > 5:
             args.steps = 5          # bounded sample: each step is ~1-4 s of CPU work

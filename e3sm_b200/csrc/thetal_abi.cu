@@ -11,12 +11,16 @@
 #include <vector>
 #include <array>
 #include <cmath>
+#include <map>
+#include <set>
+#include <nccl.h>
 
 using namespace thetal;
 
 namespace {
 
-struct Connection { int e1, dir1, e2_lid, e2_gid, e2_pid, dir2; };
+struct Connection { int e1, e1_gid, dir1, e2_lid, e2_gid, e2_pid, dir2; };
+struct Peer { int rank, send_off, send_cnt, recv_off, recv_cnt; };
 
 struct Session {
   bool active = false;
@@ -40,6 +44,16 @@ struct Session {
   std::vector<double> hD, hDinv, hmetdet, hrmetdet, hspheremp, hrspheremp, hfcor, hphis, hmetinv,
       htensorvisc, hvec, hgradphis;
   std::vector<int> hdss;
+  // partition boundary (multi-GPU DSS): ghost element slots + per-peer entry lists
+  int nghost = 0;
+  std::vector<Peer> peers;
+  std::vector<int> hsend_idx, hrecv_idx;       // local (elem*16+pt) to send / ghost (slot*16+pt) to fill
+  int *d_send_idx = nullptr, *d_recv_idx = nullptr;
+  double *d_sendbuf = nullptr, *d_recvbuf = nullptr;
+  ncclComm_t comm = nullptr;
+  ncclUniqueId nccl_id{};
+  bool have_id = false;
+  long halo_bytes = 0, exchanges = 0;
   // device
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -119,6 +133,11 @@ void initialize_hommexx_session(void)
   CUDA_OK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
   CUDA_OK(cudaEventCreate(&S.ev0));
   CUDA_OK(cudaEventCreate(&S.ev1));
+  if (S.nranks > 1) {
+    if (!S.have_id) { fail(4, "nranks > 1 needs the ncclUniqueId of rank 0 (thetal_b200_init_comm)"); return; }
+    ncclResult_t r = ncclCommInitRank(&S.comm, S.nranks, S.nccl_id, S.rank);
+    if (r != ncclSuccess) { fail(5, std::string("ncclCommInitRank: ") + ncclGetErrorString(r)); return; }
+  }
   S.active = true;
 }
 
@@ -126,14 +145,18 @@ void finalize_hommexx_session(void)
 {
   if (!S.active) return;
   cudaDeviceSynchronize();
+  if (S.comm) { ncclCommDestroy(S.comm); S.comm = nullptr; }
   for (void *p : S.allocs) cudaFree(p);
   S.allocs.clear();
   if (S.ev0) cudaEventDestroy(S.ev0);
   if (S.ev1) cudaEventDestroy(S.ev1);
   if (S.stream) cudaStreamDestroy(S.stream);
   const int dev = S.device, rank = S.rank, nranks = S.nranks, aoe = S.abort_on_error;
+  const bool have_id = S.have_id;
+  const ncclUniqueId id = S.nccl_id;
   S = Session();
   S.device = dev; S.rank = rank; S.nranks = nranks; S.abort_on_error = aoe;
+  S.have_id = have_id; S.nccl_id = id;
 }
 
 void reset_cxx_comm(const int *f_comm) { (void)f_comm; }
@@ -141,10 +164,17 @@ void reset_cxx_comm(const int *f_comm) { (void)f_comm; }
 void thetal_b200_init_comm(const int *rank, const int *nranks, const int *device, const void *nccl_id)
 {
   S.rank = *rank; S.nranks = *nranks; S.device = *device;
-  (void)nccl_id;
-  if (S.nranks > 1) fail(4, "multi-rank halo exchange is not built in this round (replicas only)");
+  S.have_id = false;
+  if (nccl_id) { memcpy(&S.nccl_id, nccl_id, sizeof(ncclUniqueId)); S.have_id = true; }
 }
-void thetal_b200_get_nccl_id(void *out) { memset(out, 0, 128); }
+void thetal_b200_get_nccl_id(void *out)
+{
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  ncclResult_t r = ncclGetUniqueId(&id);
+  if (r != ncclSuccess) { fail(5, std::string("ncclGetUniqueId: ") + ncclGetErrorString(r)); memset(out, 0, 128); return; }
+  memcpy(out, &id, 128);
+}
 void thetal_b200_set_abort_on_error(const int *flag) { S.abort_on_error = *flag; }
 int thetal_b200_last_error(void) { return S.last_error; }
 const char *thetal_b200_last_error_msg(void) { return S.last_msg.c_str(); }
@@ -174,10 +204,10 @@ void add_connection(const int *e1_lid, const int *e1_gid, const int *e1_pos, con
           *e2_pos >= 1 && *e2_pid >= 1, "add_connection: F90 indices should start at 1");
   Connection c;
   c.e1 = *e1_lid - 1;
+  c.e1_gid = *e1_gid - 1;
   c.dir1 = *e1_pos / S.max_corner - 1;      // W=0,E=1,S=2,N=3,SW=4,SE=5,NW=6,NE=7
   c.e2_lid = *e2_lid - 1; c.e2_gid = *e2_gid - 1; c.e2_pid = *e2_pid - 1;
   c.dir2 = *e2_pos / S.max_corner - 1;
-  (void)e1_gid;
   if (*e1_pid - 1 == S.rank) S.conns.push_back(c);
 }
 
@@ -198,11 +228,25 @@ void finalize_connectivity(void)
 {
   const int nelem = S.prm.nelem;
   require(nelem > 0, "init_elements_c must precede finalize_connectivity");
+  // ghost slots for neighbours owned by other ranks, numbered in (rank, global id) order
+  std::map<std::pair<int, int>, int> ghost;
+  for (const Connection &c : S.conns)
+    if (c.e2_pid != S.rank) {
+      if (c.e2_pid < 0 || c.e2_pid >= S.nranks) { fail(4, "add_connection: neighbour rank outside the communicator"); return; }
+      ghost[{c.e2_pid, c.e2_gid}] = 0;
+    }
+  int ng = 0;
+  for (auto &g : ghost) g.second = nelem + ng++;
+  S.nghost = ng;
+  std::map<int, std::set<std::pair<int, int>>> sendset, recvset;   // per peer: (global id, point)
+  std::map<int, int> lid_of_gid;
   // slot[e][p]: contributions by kind: 0..3 = W,E,S,N edge, 4 = corner
   std::vector<std::array<int, 5>> by_kind((size_t)nelem * 16);
   for (auto &a : by_kind) a.fill(-1);
   for (const Connection &c : S.conns) {
-    if (c.e2_pid != S.rank) { fail(4, "remote connection: multi-rank halo exchange is not built in this round"); return; }
+    const bool remote = c.e2_pid != S.rank;
+    const int e2 = remote ? ghost[{c.e2_pid, c.e2_gid}] : c.e2_lid;
+    if (remote) lid_of_gid[c.e1_gid] = c.e1;
     if (c.dir1 < 4) {
       require(c.dir2 < 4, "edge connected to corner");
       int p1[4], p2[4];
@@ -210,11 +254,29 @@ void finalize_connectivity(void)
       // orientation (ConnectivityHelpers.hpp:64-67): same-side pairs and W/N, E/S are reversed
       const int a = c.dir1, b = c.dir2;
       const bool rev = (a == b) || (a == 0 && b == 3) || (a == 3 && b == 0) || (a == 1 && b == 2) || (a == 2 && b == 1);
-      for (int k = 0; k < 4; k++)
-        by_kind[(size_t)c.e1 * 16 + p1[k]][c.dir1] = c.e2_lid * 16 + p2[rev ? 3 - k : k];
+      for (int k = 0; k < 4; k++) {
+        by_kind[(size_t)c.e1 * 16 + p1[k]][c.dir1] = e2 * 16 + p2[rev ? 3 - k : k];
+        if (remote) { sendset[c.e2_pid].insert({c.e1_gid, p1[k]}); recvset[c.e2_pid].insert({c.e2_gid, p2[k]}); }
+      }
     } else {
-      by_kind[(size_t)c.e1 * 16 + corner_point(c.dir1)][4] = c.e2_lid * 16 + corner_point(c.dir2);
+      by_kind[(size_t)c.e1 * 16 + corner_point(c.dir1)][4] = e2 * 16 + corner_point(c.dir2);
+      if (remote) {
+        sendset[c.e2_pid].insert({c.e1_gid, corner_point(c.dir1)});
+        recvset[c.e2_pid].insert({c.e2_gid, corner_point(c.dir2)});
+      }
     }
+  }
+  S.peers.clear(); S.hsend_idx.clear(); S.hrecv_idx.clear();
+  for (auto &ps : sendset) {
+    Peer pr;
+    pr.rank = ps.first;
+    pr.send_off = (int)S.hsend_idx.size();
+    for (auto &gp : ps.second) S.hsend_idx.push_back(lid_of_gid[gp.first] * 16 + gp.second);
+    pr.send_cnt = (int)ps.second.size();
+    pr.recv_off = (int)S.hrecv_idx.size();
+    for (auto &gp : recvset[pr.rank]) S.hrecv_idx.push_back(ghost[{pr.rank, gp.first}] * 16 + gp.second);
+    pr.recv_cnt = (int)recvset[pr.rank].size();
+    S.peers.push_back(pr);
   }
   // unpack order of edge_mod.F90:888-941: per i: S,N,W,E ; so SW: S,W  SE: E,S  NW: N,W  NE: N,E ; corners last
   S.hdss.assign((size_t)nelem * 48, -1);
@@ -379,8 +441,17 @@ void init_functors_c(const int *allocate_buffer)
   CUDA_OK(cudaMemcpy(dd, S.hdss.data(), S.hdss.size() * sizeof(int), cudaMemcpyHostToDevice));
   S.geo.dss_src = dd;
   for (int t = 0; t < NTL; t++) S.tl[t] = alloc_state(n, nlev);
-  S.tensA = alloc_state(n, nlev);
-  S.tensB = alloc_state(n, nlev);
+  S.tensA = alloc_state(n + S.nghost, nlev);      // ghost element slots behind the local elements
+  S.tensB = alloc_state(n + S.nghost, nlev);
+  if (!S.peers.empty()) {
+    const size_t nlyr = 6 * (size_t)nlev + 1;
+    S.d_send_idx = dalloc<int>(S.hsend_idx.size());
+    S.d_recv_idx = dalloc<int>(S.hrecv_idx.size());
+    CUDA_OK(cudaMemcpy(S.d_send_idx, S.hsend_idx.data(), S.hsend_idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMemcpy(S.d_recv_idx, S.hrecv_idx.data(), S.hrecv_idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+    S.d_sendbuf = dalloc<double>(S.hsend_idx.size() * nlyr);
+    S.d_recvbuf = dalloc<double>(S.hrecv_idx.size() * nlyr);
+  }
   S.der.vn0 = dalloc<double>((size_t)n * 32 * nlev);
   S.der.eta_dot_dpdn = dalloc<double>((size_t)n * 16 * (nlev + 1));
   S.der.omega_p = dalloc<double>((size_t)n * 16 * nlev);
@@ -441,6 +512,28 @@ struct ProfScope {   // per-family device time when thetal_b200_profile_step is 
   }
 };
 
+// ---- bndry_exchangeV (bndry_mod.F90:51-169) for one DSS: pack the partition-boundary points of
+// `t`, ncclSend/ncclRecv with every neighbour rank, unpack into the ghost slots of `t`.
+// nk levels of each field (+ w_i(nlevp) when wbot); all on S.stream, so it is ordered between the
+// kernel that produced `t` and the DSS kernel that gathers from it.
+#define NCCL_OK(x) do { ncclResult_t r_ = (x); if (r_ != ncclSuccess) { fail(5, std::string(#x) + ": " + ncclGetErrorString(r_)); } } while (0)
+void halo_exchange(const StatePtrs &t, int nk, int wbot)
+{
+  if (S.peers.empty()) return;
+  const int nlev = S.nlev, nlyr = 6 * nk + wbot;
+  launch_halo_pack(t, S.d_send_idx, (int)S.hsend_idx.size(), nk, wbot, nlev, S.d_sendbuf, S.stream);
+  NCCL_OK(ncclGroupStart());
+  for (const Peer &p : S.peers) {
+    NCCL_OK(ncclSend(S.d_sendbuf + (size_t)p.send_off * nlyr, (size_t)p.send_cnt * nlyr, ncclDouble, p.rank, S.comm, S.stream));
+    NCCL_OK(ncclRecv(S.d_recvbuf + (size_t)p.recv_off * nlyr, (size_t)p.recv_cnt * nlyr, ncclDouble, p.rank, S.comm, S.stream));
+  }
+  NCCL_OK(ncclGroupEnd());
+  launch_halo_unpack(t, S.d_recv_idx, (int)S.hrecv_idx.size(), nk, wbot, nlev, S.d_recvbuf, S.stream);
+  S.launches += 2;
+  S.exchanges += 1;
+  S.halo_bytes += (long)(S.hsend_idx.size() + S.hrecv_idx.size()) * nlyr * 8;
+}
+
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
 void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3)
 {
@@ -448,6 +541,7 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
   a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
   a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
   { ProfScope ps(0); launch_caar_pre(a, S.stream); }
+  { ProfScope ps(5); halo_exchange(S.tensA, S.nlev, 1); }
   DssArgs d;
   d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
   d.do_limiter = (s3 != 0.0);
@@ -478,7 +572,9 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
     a.dt = dt2 / hvs;
     a.th_is_theta = ic > 0; a.last_subcycle = (ic == hvs - 1);
     a.nu_ratio = nu_ratio1; a.tin = S.tensB; a.tout = S.tensA; launch_hv(0, a, S.stream);
+    halo_exchange(S.tensA, S.nlev, 0);
     a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB; launch_hv(1, a, S.stream);
+    halo_exchange(S.tensB, S.nlev, 0);
     a.tin = S.tensB; a.tout = S.tensA; launch_hv(2, a, S.stream);
     S.launches += 3;
   }
@@ -488,6 +584,7 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
     for (int ic = 0; ic < nt_; ic++) {
       a.dt = dt2 / nt_; a.th_is_theta = 0; a.last_subcycle = 0;
       a.tin = S.tensB; a.tout = S.tensA; launch_hv(3, a, S.stream);
+      halo_exchange(S.tensA, S.prm.nlev_tom, 0);
       a.tin = S.tensA; a.tout = S.tensB; launch_hv(4, a, S.stream);
       S.launches += 2;
     }
@@ -675,6 +772,26 @@ void thetal_b200_sync(void)
   check_device_errors("thetal_b200_sync");
 }
 long thetal_b200_launch_count(void) { return S.launches; }
+
+// Partition-boundary tables built by finalize_connectivity (host only, no device needed): used by the
+// CPU tests of the multi-rank host logic and by drivers that want to report halo sizes.
+void thetal_b200_halo_counts(int *nghost, int *npeers, int *nsend, int *nrecv)
+{
+  *nghost = S.nghost; *npeers = (int)S.peers.size();
+  *nsend = (int)S.hsend_idx.size(); *nrecv = (int)S.hrecv_idx.size();
+}
+void thetal_b200_halo_lists(int *peer_rank, int *send_off, int *send_cnt, int *recv_off, int *recv_cnt,
+                            int *send_idx, int *recv_idx)
+{
+  for (size_t i = 0; i < S.peers.size(); i++) {
+    peer_rank[i] = S.peers[i].rank; send_off[i] = S.peers[i].send_off; send_cnt[i] = S.peers[i].send_cnt;
+    recv_off[i] = S.peers[i].recv_off; recv_cnt[i] = S.peers[i].recv_cnt;
+  }
+  memcpy(send_idx, S.hsend_idx.data(), S.hsend_idx.size() * sizeof(int));
+  memcpy(recv_idx, S.hrecv_idx.data(), S.hrecv_idx.size() * sizeof(int));
+}
+void thetal_b200_dss_table(int *dss_src) { memcpy(dss_src, S.hdss.data(), S.hdss.size() * sizeof(int)); }
+void thetal_b200_halo_stats(long *exchanges, long *bytes) { *exchanges = S.exchanges; *bytes = S.halo_bytes; }
 
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);

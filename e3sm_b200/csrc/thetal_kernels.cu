@@ -1149,4 +1149,61 @@ void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStr
   wbc_kernel<<<(nelem * 16 + 255) / 256, 256, 0, st>>>(s, geo, nelem, nlev);
 }
 
+// ==========================================================================================
+// Halo pack / unpack for the multi-GPU DSS (edgeVpack / edgeVunpack, edge_mod.F90:500-629,
+// 862-944; bndry_exchangeV, bndry_mod.F90:51-169).  The DSS kernels pull their neighbours'
+// pre-DSS values straight out of the `tens` arrays; a neighbour owned by another rank is a ghost
+// element slot behind the local ones, and only its shared edge/corner points are ever filled.
+// One entry = one (element, point) on the partition boundary; its message is all layers of the
+// exchange: levels k < nk of v1, v2, dp3d, vtheta_dp, w_i, phinh_i (+ w_i(nlevp) if wbot).
+// ==========================================================================================
+__device__ __forceinline__ double *halo_addr(const StatePtrs &t, int ep, int layer, int nk, int nlev)
+{
+  const size_t e = (size_t)(ep >> 4);
+  const int p = ep & 15, nlevp = nlev + 1;
+  if (layer == 6 * nk) return t.w + e * 16 * nlevp + (size_t)nlev * 16 + p;
+  const int f = layer / nk, k = layer - f * nk;
+  switch (f) {
+    case 0: return t.v + e * 32 * nlev + (size_t)k * 32 + p;
+    case 1: return t.v + e * 32 * nlev + (size_t)k * 32 + 16 + p;
+    case 2: return t.dp + e * 16 * nlev + (size_t)k * 16 + p;
+    case 3: return t.th + e * 16 * nlev + (size_t)k * 16 + p;
+    case 4: return t.w + e * 16 * nlevp + (size_t)k * 16 + p;
+    default: return t.phi + e * 16 * nlevp + (size_t)k * 16 + p;
+  }
+}
+
+__global__ void __launch_bounds__(256) halo_pack_kernel(StatePtrs t, const int *idx, int nent, int nk, int wbot,
+                                                        int nlev, double *buf)
+{
+  const int nlyr = 6 * nk + wbot;
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)nent * nlyr) return;
+  const int ent = (int)(i / nlyr), layer = (int)(i - (long)ent * nlyr);
+  buf[i] = *halo_addr(t, idx[ent], layer, nk, nlev);
+}
+
+__global__ void __launch_bounds__(256) halo_unpack_kernel(StatePtrs t, const int *idx, int nent, int nk, int wbot,
+                                                          int nlev, const double *buf)
+{
+  const int nlyr = 6 * nk + wbot;
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)nent * nlyr) return;
+  const int ent = (int)(i / nlyr), layer = (int)(i - (long)ent * nlyr);
+  *halo_addr(t, idx[ent], layer, nk, nlev) = buf[i];
+}
+
+void launch_halo_pack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev, double *buf,
+                      cudaStream_t st)
+{
+  const long n = (long)nent * (6 * nk + wbot);
+  if (n > 0) halo_pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, idx, nent, nk, wbot, nlev, buf);
+}
+void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev,
+                        const double *buf, cudaStream_t st)
+{
+  const long n = (long)nent * (6 * nk + wbot);
+  if (n > 0) halo_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, idx, nent, nk, wbot, nlev, buf);
+}
+
 }  // namespace thetal

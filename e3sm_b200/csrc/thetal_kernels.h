@@ -57,6 +57,10 @@ void launch_caar_dss_post(const DssArgs &A, cudaStream_t st);
 void launch_dirk(const DirkArgs &A, cudaStream_t st);
 void launch_hv(int which, const HvArgs &A, cudaStream_t st);   // 0 laplace1, 1 laplace2, 2 update, 3 sponge laplace, 4 sponge update
 void launch_combo(const ComboArgs &A, cudaStream_t st);
+void launch_halo_pack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev, double *buf,
+                      cudaStream_t st);
+void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev,
+                        const double *buf, cudaStream_t st);
 void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st);
 
 }  // namespace thetal

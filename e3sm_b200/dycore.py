@@ -33,11 +33,12 @@ def _pp(a):
     return byref(c_void_p(a.ctypes.data))
 
 
-def connections(grid):
-    """GridEdge list of (e1, dir1, e2, dir2), 0-based elements, dir codes W,E,S,N,SW,SE,NW,NE = 0..7
-    (what init_cxx_connectivity feeds add_connection, prim_cxx_driver_base.F90:137-197)."""
+def connections(grid, e0=0, e1=None):
+    """GridEdge list of (e1, dir1, e2, dir2) for the elements e0 <= e1 < e1 of the storage order,
+    0-based, dir codes W,E,S,N,SW,SE,NW,NE = 0..7 (what init_cxx_connectivity feeds add_connection,
+    prim_cxx_driver_base.F90:137-197)."""
     src = grid.dss_src
-    nelem = grid.nelem
+    e1 = grid.nelem if e1 is None else e1
     out = []
 
     def edge_of(p):
@@ -52,7 +53,7 @@ def connections(grid):
     corner_dir = {0: 4, 3: 5, 12: 6, 15: 7}
     # edge connections: use the two interior points of each edge
     probes = {0: (4, 8), 1: (7, 11), 2: (1, 2), 3: (13, 14)}
-    for e in range(nelem):
+    for e in range(e0, e1):
         edge_nbr = {}
         for d, (pa, pb) in probes.items():
             sa = int(src[e, pa, 0])
@@ -72,16 +73,26 @@ def connections(grid):
 
 
 class ThetaLDycore:
-    """One rank <-> one GPU; state lives on the device between calls."""
+    """One rank <-> one GPU; state lives on the device between calls.
 
-    def __init__(self, grid, hv, params, phis, gradphis, ref_states, device=0):
+    Multi-GPU: pass the space-filling-curve ``part`` (partition.Partition; ``grid`` must be stored in
+    ``part.order``), this rank and the 128-byte ncclUniqueId of rank 0.  ``phis``, ``gradphis``,
+    ``ref_states`` and every State are then the LOCAL slices [e0:e1) of this rank."""
+
+    def __init__(self, grid, hv, params, phis, gradphis, ref_states, device=0, rank=0, part=None,
+                 nccl_id=None, host_only=False):
         self.L = _libmod.load()
         L = self.L
         self.grid, self.hv, self.params = grid, hv, params
-        self.nelem, self.nlev = grid.nelem, hv.nlev
+        self.rank, self.part = rank, part
+        nranks = 1 if part is None else part.npart
+        self.e0, self.e1 = (0, grid.nelem) if part is None else part.local_range(rank)
+        self.nelem, self.nlev = self.e1 - self.e0, hv.nlev
         L.finalize_hommexx_session()
-        L.thetal_b200_init_comm(_ci(0), _ci(1), _ci(device), None)
-        L.initialize_hommexx_session()
+        idbuf = None if nccl_id is None else ctypes.create_string_buffer(bytes(nccl_id), 128)
+        L.thetal_b200_init_comm(_ci(rank), _ci(nranks), _ci(device), idbuf)
+        if not host_only:
+            L.initialize_hommexx_session()
         self._check()
         L.thetal_b200_set_nlev(_ci(hv.nlev))
         p = params
@@ -99,14 +110,19 @@ class ThetaLDycore:
         L.init_hvcoord_c(_cd(hv.ps0), _pp(hv.hyam), _pp(hv.hyai), _pp(hv.hybm), _pp(hv.hybi))
         L.init_elements_c(_ci(self.nelem))
         L.init_time_level_c(_ci(1), _ci(2), _ci(3), _ci(0), _ci(0))
-        # connectivity (all on rank 1 / pid 1, max_corner_elem = 1)
+        # connectivity: local ids are offsets into the owner's slice of the curve, pids are ranks+1,
+        # max_corner_elem = 1
         L.init_connectivity(_ci(self.nelem), _ci(1))
         add = L.add_connection
-        one = _ci(1)
-        for (e1, d1, e2, d2) in connections(grid):
-            add(_ci(e1 + 1), _ci(int(grid.gnum[e1]) + 1), _ci(d1 + 1), one,
-                _ci(e2 + 1), _ci(int(grid.gnum[e2]) + 1), _ci(d2 + 1), one)
+        owner = np.zeros(grid.nelem, dtype=np.int64) if part is None else part.owner
+        start = np.zeros(2, dtype=np.int64) if part is None else part.start
+        for (e1, d1, e2, d2) in connections(grid, self.e0, self.e1):
+            p2 = int(owner[e2])
+            add(_ci(e1 - self.e0 + 1), _ci(int(grid.gnum[e1]) + 1), _ci(d1 + 1), _ci(rank + 1),
+                _ci(e2 - int(start[p2]) + 1), _ci(int(grid.gnum[e2]) + 1), _ci(d2 + 1), _ci(p2 + 1))
         L.finalize_connectivity()
+        if host_only:
+            return
         dvv = np.ascontiguousarray(grid.dvv)
         mp = np.ascontiguousarray(grid.mp)
         L.init_reference_element_c(_pp(dvv), _pp(mp))
@@ -115,11 +131,12 @@ class ThetaLDycore:
         gradphis = np.ascontiguousarray(gradphis)
         phis = np.ascontiguousarray(phis)
         for e in range(self.nelem):
-            L.init_elements_2d_c(_ci(e), _pp(grid.D[e]), _pp(grid.Dinv[e]), _pp(grid.fcor[e]),
-                                 _pp(grid.spheremp[e]), _pp(grid.rspheremp[e]), _pp(grid.metdet[e]),
-                                 _pp(grid.metinv[e]), _pp(grid.tensorvisc[e]), _pp(grid.vec_sph2cart[e]),
+            g = e + self.e0
+            L.init_elements_2d_c(_ci(e), _pp(grid.D[g]), _pp(grid.Dinv[g]), _pp(grid.fcor[g]),
+                                 _pp(grid.spheremp[g]), _pp(grid.rspheremp[g]), _pp(grid.metdet[g]),
+                                 _pp(grid.metinv[g]), _pp(grid.tensorvisc[g]), _pp(grid.vec_sph2cart[g]),
                                  cart.ctypes.data_as(POINTER(c_double)), ll.ctypes.data_as(POINTER(c_double)),
-                                 _pp(grid.tensorvisc[e]))
+                                 _pp(grid.tensorvisc[g]))
             L.init_geopotential_c(_ci(e), _pp(phis[e]), _pp(gradphis[e]))
         L.init_functors_c(_ci(1))
         L.init_boundary_exchanges_c()
@@ -197,18 +214,65 @@ class ThetaLDycore:
     def launch_count(self):
         return int(self.L.thetal_b200_launch_count())
 
+    def halo_tables(self):
+        """Partition-boundary tables of this rank (host side): dict with nghost, peers
+        [(rank, send_off, send_cnt, recv_off, recv_cnt)], send_idx, recv_idx, dss_src[nelem,16,3]."""
+        L = self.L
+        ng, npeer, ns, nr = c_int(0), c_int(0), c_int(0), c_int(0)
+        L.thetal_b200_halo_counts(byref(ng), byref(npeer), byref(ns), byref(nr))
+        arr = [np.zeros(max(npeer.value, 1), dtype=np.int32) for _ in range(5)]
+        sidx = np.zeros(max(ns.value, 1), dtype=np.int32)
+        ridx = np.zeros(max(nr.value, 1), dtype=np.int32)
+        L.thetal_b200_halo_lists(*[c_void_p(a.ctypes.data) for a in arr], c_void_p(sidx.ctypes.data),
+                                 c_void_p(ridx.ctypes.data))
+        dss = np.zeros((self.nelem, 16, 3), dtype=np.int32)
+        L.thetal_b200_dss_table(c_void_p(dss.ctypes.data))
+        peers = [tuple(int(a[i]) for a in arr) for i in range(npeer.value)]
+        return {"nghost": ng.value, "peers": peers, "send_idx": sidx[:ns.value], "recv_idx": ridx[:nr.value],
+                "dss_src": dss}
+
+    def halo_stats(self):
+        ex, by = ctypes.c_long(0), ctypes.c_long(0)
+        self.L.thetal_b200_halo_stats(byref(ex), byref(by))
+        return ex.value, by.value
+
     def close(self):
         self.L.finalize_hommexx_session()
 
 
-def build_case(params, hv_ref_profiles=None):
-    """Geometry + JW initial state + reference states for a SimParams config (host side)."""
+def build_case(params, hv_ref_profiles=None, part=None, rank=0):
+    """Geometry + JW initial state + reference states for a SimParams config (host side).
+
+    With ``part`` the grid is stored along the space-filling curve and the state, phis, gradphis and
+    reference states returned are this rank's slice only (the geometry stays global: it is small and
+    the DSS of spheremp/gradphis needs the neighbours)."""
     from .geometry import CubedSphere
     from .hvcoord import HVCoord
-    from .initial import jw_baroclinic, model_init2
-    grid = CubedSphere(params.ne)
+    from .initial import jw_baroclinic, jw_phis, model_init2, make_c0, gradient_sphere
     hv = HVCoord.from_table(params.nlev)
-    st, phis = jw_baroclinic(grid, hv, params.u_perturb)
     hvr = params.hv_ref_profiles if hv_ref_profiles is None else hv_ref_profiles
-    gradphis, theta_ref, dp_ref, phi_ref = model_init2(grid, hv, st, phis, hvr)
+    if part is None:
+        grid = CubedSphere(params.ne)
+        st, phis = jw_baroclinic(grid, hv, params.u_perturb)
+        gradphis, theta_ref, dp_ref, phi_ref = model_init2(grid, hv, st, phis, hvr)
+        return grid, hv, st, phis, gradphis, (theta_ref, dp_ref, phi_ref)
+    grid = CubedSphere(params.ne, order=part.order)
+    e0, e1 = part.local_range(rank)
+    gradphis_all = make_c0(grid, gradient_sphere(grid, jw_phis(grid)))
+    loc = grid.local_view(e0, e1)
+    st, phis = jw_baroclinic(loc, hv, params.u_perturb)
+    gradphis, theta_ref, dp_ref, phi_ref = model_init2(loc, hv, st, phis, hvr,
+                                                       gradphis=np.ascontiguousarray(gradphis_all[e0:e1]))
     return grid, hv, st, phis, gradphis, (theta_ref, dp_ref, phi_ref)
+
+
+def broadcast_nccl_id(td, rank):
+    """ncclUniqueId of rank 0 to every rank over the torch.distributed process group ``td``."""
+    import torch
+    buf = ctypes.create_string_buffer(128)
+    if rank == 0:
+        _libmod.load().thetal_b200_get_nccl_id(buf)
+    dev = "cuda" if td.get_backend() == "nccl" else "cpu"
+    t = torch.tensor(list(buf.raw), dtype=torch.uint8, device=dev)
+    td.broadcast(t, src=0)
+    return bytes(t.cpu().tolist())

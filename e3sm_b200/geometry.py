@@ -335,5 +335,16 @@ class CubedSphere:
         self.nnodes = int(self.node_id.max()) + 1
         self.rspheremp = 1.0 / dss_numpy(self.spheremp, self.dss_src)    # mass_matrix_mod.F90:100-114
 
+    def local_view(self, e0, e1):
+        """Per-element arrays of the storage slice [e0:e1) (what one rank of the SFC partition owns)."""
+        class _View:
+            pass
+        v = _View()
+        v.nelem, v.rearth, v.ne = e1 - e0, self.rearth, self.ne
+        for name in ("lat", "lon", "D", "Dinv", "metinv", "metdet", "rmetdet", "fcor", "spheremp",
+                     "rspheremp", "gnum", "cart"):
+            setattr(v, name, getattr(self, name)[e0:e1])
+        return v
+
     def sphere_area(self):
         return float(self.spheremp.sum())

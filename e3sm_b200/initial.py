@@ -115,6 +115,16 @@ def reference_states(hv, phis, hv_ref_profiles=0):
     return theta_ref, dp_ref, phi_ref
 
 
+def jw_phis(grid):
+    """Surface geopotential of the JW test alone (baroclinic_inst_mod.F90:168-176) -> phis[e,16]."""
+    u0, eta_s, eta_0 = 35.0, 1.0, 0.252
+    snlat, cslat = np.sin(grid.lat), np.cos(grid.lat)
+    trm2 = -2.0 * snlat ** 6 * (cslat ** 2 + 1.0 / 3.0) + 10.0 / 63.0
+    trm4 = (1.60 * cslat ** 3 * (snlat ** 2 + 2.0 / 3.0) - DD_PI * 0.25) * grid.rearth * OMEGA
+    s1 = u0 * (np.cos((eta_s - eta_0) * DD_PI * 0.5)) ** 1.5
+    return s1 * (trm2 * s1 + trm4)
+
+
 def jw_baroclinic(grid, hv, u_perturb=1.0):
     """Jablonowski-Williamson baroclinic wave (baroclinic_inst_mod.F90:57-197) -> (State, phis[e,16])."""
     nelem, nlev = grid.nelem, hv.nlev
@@ -156,9 +166,11 @@ def jw_baroclinic(grid, hv, u_perturb=1.0):
     return st, phis
 
 
-def model_init2(grid, hv, st, phis, hv_ref_profiles=0, n0=0):
-    """model_init2 (model_init_mod.F90:36-101): gradphis, w b.c., phinh_i(nlevp)=phis, reference states."""
-    gradphis = make_c0(grid, gradient_sphere(grid, phis))                             # [e,2,16]
+def model_init2(grid, hv, st, phis, hv_ref_profiles=0, n0=0, gradphis=None):
+    """model_init2 (model_init_mod.F90:36-101): gradphis, w b.c., phinh_i(nlevp)=phis, reference states.
+    ``gradphis`` may be passed in (a rank's slice of the globally DSS'd field)."""
+    if gradphis is None:
+        gradphis = make_c0(grid, gradient_sphere(grid, phis))                         # [e,2,16]
     nlev = hv.nlev
     st.w_i[:, n0, nlev] = (st.v[:, n0, nlev - 1, 0] * gradphis[:, 0] + st.v[:, n0, nlev - 1, 1] * gradphis[:, 1]) / G
     for t in range(3):

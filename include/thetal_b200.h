@@ -128,6 +128,14 @@ double thetal_b200_time_steps(const double *dt, const int *nsteps, int *nm1, int
 /* average per-kernel-family device time (ms) of the last thetal_b200_time_steps call:
  * out[0]=caar_pre out[1]=dss_post out[2]=dirk out[3]=hypervis(all) out[4]=combine; returns launches */
 long thetal_b200_launch_count(void);
+/* partition boundary built by finalize_connectivity (edge_mod.F90 putmapP/getmapP + schedule_mod.F90:37-280
+   equivalents): ghost element slots, per-peer send/recv entry lists (elem*16+point), the DSS gather table
+   [nelem][16][3], and counters of the exchanges done so far.  Host only; no device needed. */
+void thetal_b200_halo_counts(int *nghost, int *npeers, int *nsend, int *nrecv);
+void thetal_b200_halo_lists(int *peer_rank, int *send_off, int *send_cnt, int *recv_off, int *recv_cnt,
+                            int *send_idx, int *recv_idx);
+void thetal_b200_dss_table(int *dss_src);
+void thetal_b200_halo_stats(long *exchanges, long *bytes);
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);
 
