@@ -101,6 +101,13 @@ __device__ __forceinline__ double vort_finish(const Pt &t, const double *svco1, 
   return (ddx(t, svco2) - ddy(t, svco1)) * t.rmetdet_sfi;
 }
 
+// Ask the memory system to pull `bytes` (multiple of 16, 16-byte aligned) into L2 ahead of use; costs
+// no registers, unlike an early load.
+__device__ __forceinline__ void prefetch_l2(const void *ptr, unsigned bytes)
+{
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+}
+
 // EOS:175-183  pnh = p0*(p_over_exner/p0)^(1/(1-kappa))
 __device__ __forceinline__ double eos_pnh(double p_over_exner)
 {
@@ -137,6 +144,19 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   double *sdiv = sexn + 16 * nlev;
   double *scr = sdiv + 16 * nlev + (tid >> 4) * (CAAR_SLOTS * 16);   // this half-warp's tiles
 
+  // the nm1 columns are only needed by the final update of each level (PA:1674-1690), and the
+  // derived accumulators by their read-modify-write: start them towards L2 now
+  if (tid < 7) {
+    const unsigned bv = 32u * nlev * 8u, bm = 16u * nlev * 8u, bi = 16u * nlevp * 8u;
+    const bool other = A.nm1.v != A.n0.v;
+    if (tid == 0 && other) prefetch_l2(A.nm1.v + (size_t)ie * 32 * nlev, bv);
+    if (tid == 1 && other) prefetch_l2(A.nm1.dp + (size_t)ie * 16 * nlev, bm);
+    if (tid == 2 && other) prefetch_l2(A.nm1.th + (size_t)ie * 16 * nlev, bm);
+    if (tid == 3 && other) prefetch_l2(A.nm1.w + (size_t)ie * 16 * nlevp, bi);
+    if (tid == 4 && other) prefetch_l2(A.nm1.phi + (size_t)ie * 16 * nlevp, bi);
+    if (tid == 5 && A.eta_ave_w != 0.0) prefetch_l2(A.der.vn0 + (size_t)ie * 32 * nlev, bv);
+    if (tid == 6 && A.eta_ave_w != 0.0) prefetch_l2(A.der.omega_p + (size_t)ie * 16 * nlev, bm);
+  }
   // ---- phase 0: stage the n0 columns of this element (contiguous per field) ----
   {
     const double *gv = A.n0.v + (size_t)ie * 32 * nlev, *gdp = A.n0.dp + (size_t)ie * 16 * nlev;
@@ -382,7 +402,7 @@ __device__ void limiter_columns(const StatePtrs &out, int ie, int nlev, int p, d
 
 constexpr int DSS_THREADS = 256;
 
-__global__ void __launch_bounds__(DSS_THREADS) caar_dss_post_kernel(const DssArgs A)
+__global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const DssArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
   const int ie = blockIdx.x, tid = threadIdx.x, p = tid & 15, kslot = tid >> 4;
@@ -459,10 +479,13 @@ void launch_caar_dss_post(const DssArgs &A, cudaStream_t st)
 
 constexpr int DIRK_THREADS = 256;
 constexpr int DIRK_ARRAYS = 6;
+#ifndef DIRK_MINB
+#define DIRK_MINB 4
+#endif
 
 __host__ __device__ inline size_t dirk_smem_bytes(int nlev)
 {
-  return sizeof(double) * (16 * ((size_t)DIRK_ARRAYS * nlev + 1) + 64);
+  return sizeof(double) * (16 * ((size_t)DIRK_ARRAYS * nlev + 1) + 144);
 }
 
 __device__ __forceinline__ double block_max(double v, double *red, int tid)
@@ -497,7 +520,7 @@ __device__ __forceinline__ double gwphis_at(const double *v, const double *dp, i
 //  * the tridiagonal solve multiplies by reciprocals of the pivots (the solve only steers Newton);
 //  * the EOS after the last Newton update is skipped (its result is never used, IM:324-336).
 template <int ITEMS>
-__global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : 3)) dirk_kernel(const DirkArgs A)
+__global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) dirk_kernel(const DirkArgs A)
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
@@ -507,6 +530,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : 3)) dirk_kerne
   double *red = sx + n16 + 16;
   const double g = G_GRAV, dt2 = A.dt2;
   const double ptop = A.prm.ptop;
+  const int medge = (nlev >> 1) - 1;       // last row of the downward Thomas sweep
 
   const double *gth = A.np1.th + (size_t)ie * n16, *gdp = A.np1.dp + (size_t)ie * n16;
   const double *gv = A.np1.v + (size_t)ie * 2 * n16;
@@ -625,7 +649,9 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : 3)) dirk_kerne
       if (dphi > 0) bad = 1;
       const double pnh = eos_pnh(rth[j] / (-dphi));                                 // IM:261
       spnh[q] = pnh;
-      sc[q] = pnh / dphi;
+      const double cq = pnh / dphi;
+      sc[q] = cq;
+      if ((q >> 4) == medge) red[64 + p] = cq;
     }
   }
   __syncthreads();
@@ -651,37 +677,106 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : 3)) dirk_kerne
       }
     }
     __syncthreads();
-    // tridiagonal solve J x = -Fn: Jacobian rows (IM:414-433) assembled on the fly from c = pnh/dphi
-    // and b = a/dp_i; Thomas sweeps (IM:590-598) with reciprocal pivots, one column per lane.
-    if (tid < 16) {
-      double cprev = sc[p];
-      double Uprev = 2 * (ajac * srdpi[p]) * cprev;
-      double r = 1.0 / (1 - Uprev);
-      double y = sx[p];
-      sx[p] = y * r; sc[p] = Uprev * r;
-      double cn = sc[16 + p], bn = ajac * srdpi[16 + p], rn = sx[16 + p];
-      for (int k = 1; k < nlev; k++) {
-        const int q = k * 16 + p;
-        const double c = cn, b = bn, rhs = rn;
-        if (k + 1 < nlev) { cn = sc[q + 16]; bn = ajac * srdpi[q + 16]; rn = sx[q + 16]; }
-        const double L = b * cprev, U = b * c;
-        const double diag = 1 - L - U;
-        const double LU = L * Uprev;
-        const double lr = L * r;
-        const double D = fma(-LU, r, diag);
-        y = fma(-lr, y, rhs);
-        r = 1.0 / D;
-        sx[q] = y * r; sc[q] = U * r;
-        Uprev = U; cprev = c;
+    // tridiagonal solve J x = -Fn.  Jacobian rows (IM:414-433) are assembled on the fly from
+    // c = pnh/dphi and b = a/dp_i.  The Thomas recurrence (IM:590-598) is run from both ends at once:
+    // warp 0 eliminates rows 0..m-1 downwards, warp 1 rows nlev-1..m upwards (same arithmetic with
+    // the sub- and super-diagonal swapped); the reduced rows m-1 and m form a 2x2 system, then both
+    // back-substitute away from the middle.  Rows are stored normalised (x_k + sc_k x_next = sx_k),
+    // so back-substitution is one FMA per row.  One column per lane (16 lanes of each warp).
+    if (tid < 64) {
+      const int m = nlev >> 1;
+      const bool up = tid >= 32;
+      double myc = 0.0, myy = 0.0;
+      if ((tid & 31) < 16) {
+        if (!up) {
+          const double *pc = sc + p, *pd = srdpi + p;
+          double *wc = sc + p, *wx = sx + p;
+          double cprev = pc[0];
+          double Uprev = 2 * (ajac * pd[0]) * cprev;
+          double r = 1.0 / (1 - Uprev);
+          double y = wx[0];
+          myc = Uprev * r; myy = y * r;
+          wc[0] = myc; wx[0] = myy;
+          double cn = pc[16], bn = ajac * pd[16], rn = wx[16];
+          for (int k = 1; k < m; k++) {
+            pc += 16; pd += 16; wc += 16; wx += 16;
+            const double c = cn, b = bn, rhs = rn;
+            if (k + 1 < m) { cn = pc[16]; bn = ajac * pd[16]; rn = wx[16]; }
+            const double L = b * cprev, U = b * c;
+            const double diag = 1 - L - U;
+            const double P = fma(-(L * Uprev), r, diag);
+            y = fma(-(L * r), y, rhs);
+            r = 1.0 / P;
+            myc = U * r; myy = y * r;
+            wc[0] = myc; wx[0] = myy;
+            Uprev = U; cprev = c;
+          }
+        } else {
+          const int q0 = (nlev - 1) * 16 + p;
+          const double c_edge = red[64 + p];            // c_{m-1}, saved where c is computed
+          const double *pc = sc + q0, *pd = srdpi + q0;
+          double *wc = sc + q0, *wx = sx + q0;
+          double c = pc[0];
+          double cm1 = (nlev - 2 >= m) ? pc[-16] : c_edge;
+          const double b0 = ajac * pd[0];
+          double Lprev = b0 * cm1;
+          double r = 1.0 / (1 - Lprev - b0 * c);
+          double y = wx[0];
+          myc = Lprev * r; myy = y * r;
+          wc[0] = myc; wx[0] = myy;
+          double bn = 0.0, rn = 0.0, cn = 0.0;         // row k-1 operands: b, rhs and c_{k-2}
+          if (nlev - 2 >= m) { bn = ajac * pd[-16]; rn = wx[-16]; cn = (nlev - 3 >= m) ? pc[-32] : c_edge; }
+          for (int k = nlev - 2; k >= m; k--) {
+            pc -= 16; pd -= 16; wc -= 16; wx -= 16;
+            c = cm1; cm1 = cn;
+            const double b = bn, rhs = rn;
+            if (k - 1 >= m) { bn = ajac * pd[-16]; rn = wx[-16]; cn = (k - 2 >= m) ? pc[-32] : c_edge; }
+            const double L = b * cm1, U = b * c;
+            const double diag = 1 - L - U;
+            const double P = fma(-(U * Lprev), r, diag);
+            y = fma(-(U * r), y, rhs);
+            r = 1.0 / P;
+            myc = L * r; myy = y * r;
+            wc[0] = myc; wx[0] = myy;
+            Lprev = L;
+          }
+        }
+        red[(up ? 112 : 80) + p] = myc;
+        red[(up ? 128 : 96) + p] = myy;
       }
-      double x = sx[(nlev - 1) * 16 + p];
-      double un = sc[(nlev - 2) * 16 + p], yn = sx[(nlev - 2) * 16 + p];
-      for (int k = nlev - 2; k >= 0; k--) {
-        const int q = k * 16 + p;
-        const double u = un, yy = yn;
-        if (k > 0) { un = sc[q - 16]; yn = sx[q - 16]; }
-        x = fma(-u, x, yy);
-        sx[q] = x;
+      asm volatile("bar.sync 1, 64;" ::: "memory");
+      if ((tid & 31) < 16) {
+        const double cp = red[80 + p], yp = red[96 + p], lp = red[112 + p], zp = red[128 + p];
+        const double xm = (zp - lp * yp) / (1 - lp * cp);
+        if (!up) {
+          double x = yp - cp * xm;
+          double *wx = sx + (m - 1) * 16 + p;
+          const double *pc = sc + (m - 1) * 16 + p;
+          wx[0] = x;
+          double un = 0.0, yn = 0.0;
+          if (m >= 2) { un = pc[-16]; yn = wx[-16]; }
+          for (int k = m - 2; k >= 0; k--) {
+            pc -= 16; wx -= 16;
+            const double u = un, yy = yn;
+            if (k > 0) { un = pc[-16]; yn = wx[-16]; }
+            x = fma(-u, x, yy);
+            wx[0] = x;
+          }
+        } else {
+          double x = xm;
+          double *wx = sx + m * 16 + p;
+          const double *pc = sc + m * 16 + p;
+          wx[0] = x;
+          double un = 0.0, yn = 0.0;
+          if (m + 1 < nlev) { un = pc[16]; yn = wx[16]; }
+          for (int k = m + 1; k < nlev; k++) {
+            pc += 16; wx += 16;
+            const double u = un, yy = yn;
+            if (k + 1 < nlev) { un = pc[16]; yn = wx[16]; }
+            x = fma(-u, x, yy);
+            wx[0] = x;
+          }
+        }
       }
     }
     __syncthreads();
@@ -759,7 +854,9 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : 3)) dirk_kerne
         if (dphi > 0) bad = 1;
         const double pnh = eos_pnh(rth[j] / (-dphi));                               // IM:324
         spnh[q] = pnh;
-        sc[q] = pnh / dphi;
+        const double cq = pnh / dphi;
+        sc[q] = cq;
+        if ((q >> 4) == medge) red[64 + p] = cq;
       }
     }
     __syncthreads();
@@ -964,7 +1061,7 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace2_kernel(const HvArgs A)
 }
 
 // pass 3 (PA:674-758, 767-774): DSS(tin) * dt * rspheremp added to the state
-__global__ void __launch_bounds__(HV_THREADS) hv_update_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
