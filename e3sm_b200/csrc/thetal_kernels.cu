@@ -108,6 +108,32 @@ __device__ __forceinline__ void prefetch_l2(const void *ptr, unsigned bytes)
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
 }
 
+// TMA bulk copy global -> shared (cp.async.bulk, 1-D) completing on an mbarrier: one thread moves a
+// whole contiguous element column block; bytes multiple of 16, both addresses 16-byte aligned.
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned phase)
+{
+  unsigned ok;
+  do {
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+  } while (!ok);
+}
+
 // EOS:175-183  pnh = p0*(p_over_exner/p0)^(1/(1-kappa))
 __device__ __forceinline__ double eos_pnh(double p_over_exner)
 {
@@ -157,16 +183,21 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     if (tid == 5 && A.eta_ave_w != 0.0) prefetch_l2(A.der.vn0 + (size_t)ie * 32 * nlev, bv);
     if (tid == 6 && A.eta_ave_w != 0.0) prefetch_l2(A.der.omega_p + (size_t)ie * 16 * nlev, bm);
   }
-  // ---- phase 0: stage the n0 columns of this element (contiguous per field) ----
-  {
-    const double *gv = A.n0.v + (size_t)ie * 32 * nlev, *gdp = A.n0.dp + (size_t)ie * 16 * nlev;
-    const double *gth = A.n0.th + (size_t)ie * 16 * nlev;
-    const double *gw = A.n0.w + (size_t)ie * 16 * nlevp, *gphi = A.n0.phi + (size_t)ie * 16 * nlevp;
-    for (int q = tid; q < 32 * nlev; q += CAAR_THREADS) sv[q] = gv[q];
-    for (int q = tid; q < 16 * nlev; q += CAAR_THREADS) { sdp[q] = gdp[q]; sth[q] = gth[q]; }
-    for (int q = tid; q < 16 * nlevp; q += CAAR_THREADS) { sw[q] = gw[q]; sphi[q] = gphi[q]; }
-  }
+  // ---- phase 0: stage the n0 columns of this element: five TMA bulk copies (each field of an
+  // element is one contiguous block), completion counted in bytes on an mbarrier ----
+  __shared__ unsigned long long stage_bar;
+  if (tid == 0) mbar_init(&stage_bar, 1);
   __syncthreads();
+  if (tid == 0) {
+    const unsigned bv = 32u * nlev * 8u, bm = 16u * nlev * 8u, bi = 16u * nlevp * 8u;
+    mbar_expect_tx(&stage_bar, bv + 2 * bm + 2 * bi);
+    bulk_g2s(sv, A.n0.v + (size_t)ie * 32 * nlev, bv, &stage_bar);
+    bulk_g2s(sdp, A.n0.dp + (size_t)ie * 16 * nlev, bm, &stage_bar);
+    bulk_g2s(sth, A.n0.th + (size_t)ie * 16 * nlev, bm, &stage_bar);
+    bulk_g2s(sw, A.n0.w + (size_t)ie * 16 * nlevp, bi, &stage_bar);
+    bulk_g2s(sphi, A.n0.phi + (size_t)ie * 16 * nlevp, bi, &stage_bar);
+  }
+  mbar_wait(&stage_bar, 0);
   // ---- phase 1: EOS (EOS:175-183), one pow per point-level ----
   {
     int bad = 0;
@@ -199,6 +230,11 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     const bool act = kk < nlev;
     const int k = act ? kk : nlev - 1;     // inactive half-warps redo the last level, never store
     const int q = k * 16 + p;
+    // nm1 values of the final update (PA:1674-1690): issue the loads now, use them ~1000 instructions later
+    const size_t gq = (size_t)ie * 16 * nlev + q, gqv = (size_t)ie * 32 * nlev + k * 32 + p;
+    const size_t gqi = (size_t)ie * 16 * nlevp + q;
+    const double m_v1 = A.nm1.v[gqv], m_v2 = A.nm1.v[gqv + 16], m_th = A.nm1.th[gq];
+    const double m_w = A.nm1.w[gqi], m_phi = A.nm1.phi[gqi], m_dp = A.nm1.dp[gq];
     const double dp = sdp[q], th = sth[q], v1 = sv[k * 32 + p], v2 = sv[k * 32 + 16 + p];
     const double wk = sw[q], wk1 = sw[q + 16];
     const double pnh = spnh[q], exner = sexn[q];
@@ -293,14 +329,12 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
 
     if (act) {
       // PA:1674-1690  X(np1) = spheremp*(scale3*X(nm1) + dt2*tens); reads of nm1 straight from HBM
-      const size_t gq = (size_t)ie * 16 * nlev + q, gqv = (size_t)ie * 32 * nlev + k * 32 + p;
-      const size_t gqi = (size_t)ie * 16 * nlevp + q;
-      A.tens.v[gqv] = spheremp * (s3 * A.nm1.v[gqv] + dt2 * vt1);
-      A.tens.v[gqv + 16] = spheremp * (s3 * A.nm1.v[gqv + 16] + dt2 * vt2);
-      A.tens.th[gq] = spheremp * (s3 * A.nm1.th[gq] + dt2 * theta_tens);
-      A.tens.w[gqi] = spheremp * (s3 * A.nm1.w[gqi] + dt2 * w_tens);
-      A.tens.phi[gqi] = spheremp * (s3 * A.nm1.phi[gqi] + dt2 * phi_tens);
-      A.tens.dp[gq] = spheremp * (s3 * A.nm1.dp[gq] - s1 * dt2 * divdp);            // eta_dot = 0
+      A.tens.v[gqv] = spheremp * (s3 * m_v1 + dt2 * vt1);
+      A.tens.v[gqv + 16] = spheremp * (s3 * m_v2 + dt2 * vt2);
+      A.tens.th[gq] = spheremp * (s3 * m_th + dt2 * theta_tens);
+      A.tens.w[gqi] = spheremp * (s3 * m_w + dt2 * w_tens);
+      A.tens.phi[gqi] = spheremp * (s3 * m_phi + dt2 * phi_tens);
+      A.tens.dp[gq] = spheremp * (s3 * m_dp - s1 * dt2 * divdp);                    // eta_dot = 0
       if (accum) {
         sdiv[q] = divdp;
         A.der.vn0[gqv] += A.eta_ave_w * (v1 * dp);                                  // PA:1190
