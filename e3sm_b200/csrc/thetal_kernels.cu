@@ -572,6 +572,14 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
   const double gp1 = A.geo.gradphis[(size_t)ie * 32 + p], gp2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
   int bad = 0;
   double rth[ITEMS], w0[ITEMS], dphi0[ITEMS], phi0[ITEMS];
+  if (tid < 5) {      // start the element's columns towards L2 (v is only read by compute_gwphis)
+    const unsigned bv = 32u * nlev * 8u, bm = 16u * nlev * 8u, bi = 16u * nlevp * 8u;
+    if (tid == 0) prefetch_l2(gdp, bm);
+    if (tid == 1) prefetch_l2(gth, bm);
+    if (tid == 2) prefetch_l2(gw, bi);
+    if (tid == 3) prefetch_l2(gphi, bi);
+    if (tid == 4) prefetch_l2(gv, bv);
+  }
 
   // ---- load, wmax (IM:168-170) ----
   double wmax = 0.0;
@@ -1034,6 +1042,17 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace1_kernel(const HvArgs A)
   pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
   ptw_init(w, t, A.geo, ie, A.prm.rearth_inv);
   const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  if (tid < 8) {
+    const unsigned bv = 32u * nlev * 8u, bm = 16u * nlev * 8u, bi = 16u * nlevp * 8u;
+    if (tid == 0) prefetch_l2(A.st.v + ev, bv);
+    if (tid == 1) prefetch_l2(A.st.dp + em, bm);
+    if (tid == 2) prefetch_l2(A.st.th + em, bm);
+    if (tid == 3) prefetch_l2(A.st.w + ei, bi);
+    if (tid == 4) prefetch_l2(A.st.phi + ei, bi);
+    if (tid == 5) prefetch_l2(A.ref.dp_ref + em, bm);
+    if (tid == 6) prefetch_l2(A.ref.theta_ref + em, bm);
+    if (tid == 7) prefetch_l2(A.ref.phi_ref + ei, bi);
+  }
   const int niter = (nlev + KS - 1) / KS;
   for (int it = 0; it < niter; it++) {
     const int kk = it * KS + kslot;
@@ -1072,6 +1091,13 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace2_kernel(const HvArgs A)
   const double rs = A.geo.rspheremp[(size_t)ie * 16 + p];
   const size_t sm_ = 16 * (size_t)nlev, si = 16 * (size_t)nlevp, sv = 32 * (size_t)nlev;
   const size_t em = ie * sm_, ei = ie * si, ev = ie * sv;
+  if (tid < 5) {
+    if (tid == 0) prefetch_l2(A.tin.v + ev, (unsigned)(sv * 8));
+    if (tid == 1) prefetch_l2(A.tin.dp + em, (unsigned)(sm_ * 8));
+    if (tid == 2) prefetch_l2(A.tin.th + em, (unsigned)(sm_ * 8));
+    if (tid == 3) prefetch_l2(A.tin.w + ei, (unsigned)(si * 8));
+    if (tid == 4) prefetch_l2(A.tin.phi + ei, (unsigned)(si * 8));
+  }
   const int niter = (nlev + KS - 1) / KS;
   for (int it = 0; it < niter; it++) {
     const int kk = it * KS + kslot;
