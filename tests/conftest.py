@@ -72,3 +72,25 @@ def spun_up_state(case, nsteps=10, seed=20240611, perturb=1e-3):
 @pytest.fixture(scope="session")
 def parity_state_c1(case_c1):
     return spun_up_state(case_c1)
+
+
+def global_diagnostics(st, tl, grid, hv):
+    """min surface pressure, dry mass and total energy (KE + w-KE + internal + potential) of one time
+    level, in the spirit of prim_state_mod.F90:897-935 (same formula for both runs being compared)."""
+    from e3sm_b200.geometry import CP, KAPPA, P0, RGAS
+    dp, th = st.dp3d[:, tl], st.vtheta_dp[:, tl]
+    v, w, phi = st.v[:, tl], st.w_i[:, tl], st.phinh_i[:, tl]
+    ps = hv.hyai[0] * hv.ps0 + dp.sum(axis=1)                         # [e,16]
+    area = grid.spheremp
+    mass = float((ps * area).sum())
+    dphi = phi[:, 1:] - phi[:, :-1]
+    poe = RGAS * th / (-dphi)
+    pnh = P0 * (poe / P0) ** (1.0 / (1.0 - KAPPA))
+    exner = pnh / poe
+    ke = 0.5 * dp * (v[:, :, 0] ** 2 + v[:, :, 1] ** 2)
+    kew = 0.25 * dp * (w[:, :-1] ** 2 + w[:, 1:] ** 2)
+    ie = CP * th * exner + pnh * dphi
+    pe = 0.5 * dp * (phi[:, :-1] + phi[:, 1:])
+    col = (ke + kew + ie + pe).sum(axis=1) + hv.hyai[0] * hv.ps0 * phi[:, 0]
+    energy = float((col * area).sum())
+    return float(ps.min()), mass, energy

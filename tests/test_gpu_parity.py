@@ -130,6 +130,36 @@ def test_ten_steps(case_c1):
     d.close()
 
 
+def test_ten_day_baroclinic_wave_diagnostics(case_c1):
+    """North-star check: 10 simulated days of the JW baroclinic wave (C1: ne4 L26, dt=600 s, 1440
+    dynamics steps, tstep_type 9 + hyperviscosity + sponge); min surface pressure, dry mass and total
+    energy of the GPU run within 1e-6 relative of the oracle run.  Both runs are vertically
+    Lagrangian WITHOUT vertical remap (vertical_remap is next-row N1), which the coarse
+    ne4 wave tolerates for 10 days."""
+    from conftest import global_diagnostics
+    p, grid, hv, st0, phis, gradphis, refs = case_c1
+    p, o, so, d = make_pair(case_c1, st0.copy())
+    nsteps = 1440
+    nm1, n0, np1 = 0, 1, 2
+    for _ in range(nsteps):
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        nm1, n0, np1 = n0, np1, nm1
+    assert o.error_flag == 0
+    ms, g_nm1, g_n0, g_np1 = d.time_steps(p.tstep, nsteps, 0, 1, 2)
+    assert g_n0 == n0
+    sg = d.get_state()
+    dg, do = global_diagnostics(sg, n0, grid, hv), global_diagnostics(so, n0, grid, hv)
+    d0 = global_diagnostics(st0, 0, grid, hv)
+    print("10-day diagnostics (min ps, mass, energy): gpu", dg, "oracle", do, "initial", d0)
+    for a, b, name in zip(dg, do, ("min ps", "mass", "total energy")):
+        assert abs(a - b) <= 1e-6 * abs(b), (name, a, b)
+    assert abs(dg[1] - d0[1]) <= 1e-12 * d0[1]          # dry mass is conserved by the step
+    assert dg[0] < d0[0] - 100.0                         # and the wave really developed
+    for f in ("v", "vtheta_dp", "phinh_i", "dp3d"):     # the fields themselves are still close
+        assert rel_l2(getattr(sg, f)[:, n0], getattr(so, f)[:, n0]) <= 1e-6, f
+    d.close()
+
+
 def test_prim_run_subcycle(case_c1, parity_state_c1):
     """the reference entry point: rsplit dynamics steps, 1-based time levels in/out"""
     p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
