@@ -11,6 +11,7 @@
 // tensor cores).  Element columns are staged through shared memory once; DSS is a pull-style
 // gather from the neighbours' pre-DSS ("tens") values, so there are no edge buffers.
 #include "thetal_kernels.h"
+#include "thetal_pow.h"
 #include <cstdio>
 
 namespace thetal {
@@ -135,9 +136,16 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned phas
 }
 
 // EOS:175-183  pnh = p0*(p_over_exner/p0)^(1/(1-kappa))
+// 1/(1-kappa) and kappa-1 with g*log2(e) as double-doubles (thetal_pow.h)
+__device__ constexpr thetal_pow::PowConst C_GAMMA = {1.0 / (1.0 - KAPPA), 0.0, 2.0194836983862725, 1.3732662420330506e-16};
+__device__ constexpr thetal_pow::PowConst C_KM1 = {KAPPA - 1.0, 0.0, -1.0306441110016318, -8.6951363107339526e-17};
+static_assert(1.0 / (1.0 - KAPPA) == 1.3997994317232159 && KAPPA - 1.0 == -0.71438805970149244, "pow constants");
+using thetal_pow::div_fast;
+using thetal_pow::rcp46;
+
 __device__ __forceinline__ double eos_pnh(double p_over_exner)
 {
-  return P0 * pow(p_over_exner / P0, 1.0 / (1.0 - KAPPA));
+  return P0 * thetal_pow::pow_pos(div_fast(p_over_exner, P0), C_GAMMA);
 }
 
 // ==========================================================================================
@@ -205,10 +213,10 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       const double dphi = sphi[q + 16] - sphi[q];
       const double th = sth[q], dp = sdp[q];
       if (th < 0 || dp < 0 || dphi > 0) bad = 1;
-      const double poe = RGAS * th / (-dphi);
+      const double poe = div_fast(RGAS * th, -dphi);
       const double pnh = eos_pnh(poe);
       spnh[q] = pnh;
-      sexn[q] = pnh / poe;
+      sexn[q] = div_fast(pnh, poe);
     }
     if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
   }
@@ -613,7 +621,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
     for (int q = tid; q < n16; q += DIRK_THREADS) {
       const double dphi = tphi[q + 16] - tphi[q], th = tth[q], dp = tdp[q];
       if (th < 0 || dp < 0 || dphi > 0) bad = 1;
-      spnh[q] = eos_pnh(RGAS * th / (-dphi));
+      spnh[q] = eos_pnh(div_fast(RGAS * th, -dphi));
     }
     __syncthreads();
 #pragma unroll
@@ -654,7 +662,9 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
 #pragma unroll
   for (int j = 0; j < ITEMS; j++) {
     const int q = tid + j * DIRK_THREADS;
-    if (q < n16) sr[q] = (rth[j] * pow(spnh[q] / P0, KAPPA - 1)) / P0;
+    const int qq = min(q, n16 - 1);
+    const double term = div_fast(rth[j] * thetal_pow::pow_pos(div_fast(spnh[qq], P0), C_KM1), P0);
+    if (q < n16) sr[q] = term;
   }
   __syncthreads();
   if (tid < 16) {   // sr <- phi_np1 (hydrostatic), bottom-up
@@ -685,13 +695,15 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
 #pragma unroll
   for (int j = 0; j < ITEMS; j++) {
     const int q = tid + j * DIRK_THREADS;
+    const int qq = min(q, n16 - 1);           // branch-free body: the point-levels of a thread overlap
+    const double w_guess = div_fast(sr[qq] - sx[qq], dt2 * g);
+    const double dphi = spnh[qq];
+    if (q < n16 && dphi > 0) bad = 1;   // (a clamped duplicate may read a slot already overwritten)
+    const double pnh = eos_pnh(div_fast(rth[j], -dphi));                            // IM:261
+    const double cq = pnh * rcp46(dphi);
     if (q < n16) {
-      sw[q] = (sr[q] - sx[q]) / (dt2 * g);
-      const double dphi = spnh[q];
-      if (dphi > 0) bad = 1;
-      const double pnh = eos_pnh(rth[j] / (-dphi));                                 // IM:261
+      sw[q] = w_guess;
       spnh[q] = pnh;
-      const double cq = pnh / dphi;
       sc[q] = cq;
       if ((q >> 4) == medge) red[64 + p] = cq;
     }
@@ -735,7 +747,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
           double *wc = sc + p, *wx = sx + p;
           double cprev = pc[0];
           double Uprev = 2 * (ajac * pd[0]) * cprev;
-          double r = 1.0 / (1 - Uprev);
+          double r = rcp46(1 - Uprev);
           double y = wx[0];
           myc = Uprev * r; myy = y * r;
           wc[0] = myc; wx[0] = myy;
@@ -748,7 +760,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
             const double diag = 1 - L - U;
             const double P = fma(-(L * Uprev), r, diag);
             y = fma(-(L * r), y, rhs);
-            r = 1.0 / P;
+            r = rcp46(P);
             myc = U * r; myy = y * r;
             wc[0] = myc; wx[0] = myy;
             Uprev = U; cprev = c;
@@ -762,7 +774,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
           double cm1 = (nlev - 2 >= m) ? pc[-16] : c_edge;
           const double b0 = ajac * pd[0];
           double Lprev = b0 * cm1;
-          double r = 1.0 / (1 - Lprev - b0 * c);
+          double r = rcp46(1 - Lprev - b0 * c);
           double y = wx[0];
           myc = Lprev * r; myy = y * r;
           wc[0] = myc; wx[0] = myy;
@@ -777,7 +789,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
             const double diag = 1 - L - U;
             const double P = fma(-(U * Lprev), r, diag);
             y = fma(-(U * r), y, rhs);
-            r = 1.0 / P;
+            r = rcp46(P);
             myc = L * r; myy = y * r;
             wc[0] = myc; wx[0] = myy;
             Lprev = L;
@@ -789,7 +801,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
       asm volatile("bar.sync 1, 64;" ::: "memory");
       if ((tid & 31) < 16) {
         const double cp = red[80 + p], yp = red[96 + p], lp = red[112 + p], zp = red[128 + p];
-        const double xm = (zp - lp * yp) / (1 - lp * cp);
+        const double xm = (zp - lp * yp) * rcp46(1 - lp * cp);
         if (!up) {
           double x = yp - cp * xm;
           double *wx = sx + (m - 1) * 16 + p;
@@ -891,12 +903,13 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
 #pragma unroll
     for (int j = 0; j < ITEMS; j++) {
       const int q = tid + j * DIRK_THREADS;
+      const int qq = min(q, n16 - 1);
+      const double dphi = sr[qq];
+      if (q < n16 && dphi > 0) bad = 1;
+      const double pnh = eos_pnh(div_fast(rth[j], -dphi));                          // IM:324
+      const double cq = pnh * rcp46(dphi);
       if (q < n16) {
-        const double dphi = sr[q];
-        if (dphi > 0) bad = 1;
-        const double pnh = eos_pnh(rth[j] / (-dphi));                               // IM:324
         spnh[q] = pnh;
-        const double cq = pnh / dphi;
         sc[q] = cq;
         if ((q >> 4) == medge) red[64 + p] = cq;
       }

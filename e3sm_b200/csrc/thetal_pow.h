@@ -6,8 +6,9 @@
 //
 //   x = 2^e m, m in [sqrt(1/2), sqrt(2));  log m = 2 atanh(f), f = (m-1)/(m+1) kept as a
 //   double-double;  y = g e + (g log2 e) log m as a double-double;  x^g = 2^n exp((y-n) ln 2).
-// Measured on 4e7 log-uniform x in [1e-7, 1e4] against __float128 powq: <= 1 ulp (see
-// tests/test_pow.py), i.e. the same class as CUDA's pow (documented 2 ulp) and glibc's (<1 ulp).
+// Measured on 2e7 log-uniform x in [1e-7, 1e4] per exponent against __float128 powq: max 1.56 ulp
+// (glibc pow: 0.51 ulp; CUDA pow: documented 2 ulp); div_fast: 0.5 ulp on 2e7 random quotients
+// (oracle/check_pow.cpp is the harness).
 #pragma once
 #include <stdint.h>
 #include <math.h>
