@@ -215,8 +215,14 @@ def run_ours(args, world, rank, local, td):
     dom = max(nl, key=lambda k: fam_ms[k])
     dom_ms = fam_ms[dom] / nl[dom]
     ach = nelem * alg[dom] / (dom_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    if os.path.exists(tpath) and world == 1:
+        tj = json.load(open(tpath))
+        if tj.get("workload") == args.config and (dom + "_kernel") in tj:
+            traffic = tj[dom + "_kernel"]["traffic_bytes_per_launch"]
     roofline = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak, "traffic": None, "peak_kind": peak_kind,
+                "frac": ach / peak, "traffic": traffic, "peak_kind": peak_kind,
                 "alg_bytes_per_launch": nelem * alg[dom], "launch_ms": dom_ms}
     step_gbs = nelem_total * bstep / (ms / K * 1e-3) / 1e9
     # ---- end to end through the C ABI with host buffers ----

@@ -246,22 +246,22 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     const double dp = sdp[q], th = sth[q], v1 = sv[k * 32 + p], v2 = sv[k * 32 + 16 + p];
     const double wk = sw[q], wk1 = sw[q + 16];
     const double pnh = spnh[q], exner = sexn[q];
-    const double theta = th / dp;                                                  // PA:1116
+    const double theta = div_fast(th, dp);                                         // PA:1116
     // interface quantities at k (top of the layer) and k+1 (bottom)
     double dpi_k, v1i_k, v2i_k, mu_k;                                               // PA:1156-1170, EOS:198-208
     if (k == 0) {
       dpi_k = dp; v1i_k = v1; v2i_k = v2;
-      mu_k = 2 * (pnh - A.prm.ptop) / dpi_k;
+      mu_k = div_fast(2 * (pnh - A.prm.ptop), dpi_k);
     } else {
       const double dpm = sdp[q - 16];
       dpi_k = (dp + dpm) / 2;
-      v1i_k = (dp * v1 + dpm * sv[(k - 1) * 32 + p]) / (2 * dpi_k);
-      v2i_k = (dp * v2 + dpm * sv[(k - 1) * 32 + 16 + p]) / (2 * dpi_k);
-      mu_k = (pnh - spnh[q - 16]) / dpi_k;
+      v1i_k = div_fast(dp * v1 + dpm * sv[(k - 1) * 32 + p], 2 * dpi_k);
+      v2i_k = div_fast(dp * v2 + dpm * sv[(k - 1) * 32 + 16 + p], 2 * dpi_k);
+      mu_k = div_fast(pnh - spnh[q - 16], dpi_k);
     }
     double mu_k1;
-    if (k == nlev - 1) mu_k1 = 2 * ((pnh + dp / 2) - pnh) / dp;                      // EOS:193,205
-    else mu_k1 = (spnh[q + 16] - pnh) / ((sdp[q + 16] + dp) / 2);
+    if (k == nlev - 1) mu_k1 = div_fast(2 * ((pnh + dp / 2) - pnh), dp);             // EOS:193,205
+    else mu_k1 = div_fast(spnh[q + 16] - pnh, (sdp[q + 16] + dp) / 2);
 
     // tiles for the operators that act on computed quantities
     double gv1, gv2, vc1, vc2, gt1, gt2;
@@ -329,8 +329,8 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       double gl1, gl2;
       gradient_sphere(t, scr, gl1, gl2);
       const double T0 = TREF - TREF_LAPSE * TREF * CP / G_GRAV;
-      mg1 = mg1 + CP * T0 * (gl1 - ge1 / exner);
-      mg2 = mg2 + CP * T0 * (gl2 - ge2 / exner);
+      mg1 = mg1 + CP * T0 * (gl1 - div_fast(ge1, exner));
+      mg2 = mg2 + CP * T0 * (gl2 - div_fast(ge2, exner));
     }
     const double vt1 = (v2 * (fcor + vort) - ke1 - mg1 - gp1 - wv1) * s1;           // PA:1495-1506 (v_vadv = 0)
     const double vt2 = (-v1 * (fcor + vort) - ke2 - mg2 - gp2 - wv2) * s1;
@@ -546,8 +546,8 @@ __device__ __forceinline__ double gwphis_at(const double *v, const double *dp, i
                                             double g1, double g2)
 {
   const double dk = dp[k * 16 + p], dm = dp[(k - 1) * 16 + p];
-  const double vi1 = (dk * v[k * 32 + p] + dm * v[(k - 1) * 32 + p]) / (dk + dm);
-  const double vi2 = (dk * v[k * 32 + 16 + p] + dm * v[(k - 1) * 32 + 16 + p]) / (dk + dm);
+  const double vi1 = div_fast(dk * v[k * 32 + p] + dm * v[(k - 1) * 32 + p], dk + dm);
+  const double vi2 = div_fast(dk * v[k * 32 + 16 + p] + dm * v[(k - 1) * 32 + 16 + p], dk + dm);
   return (vi1 * g1 + vi2 * g2) * c_hybi[k];
 }
 
@@ -598,7 +598,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
     if (q < n16) {
       const double dp = gdp[q], th = gth[q];
       const double dpi = (q >= 16) ? (dp + gdp[q - 16]) / 2 : dp;
-      srdpi[q] = 1.0 / dpi;
+      srdpi[q] = div_fast(1.0, dpi);
       sc[q] = dp;                           // temporary: pressure scan below
       if (th < 0 || dp < 0) bad = 1;
       rth[j] = RGAS * th;
@@ -630,8 +630,8 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
       if (q < n16) {
         const int k = q >> 4;
         double mu;
-        if (k == 0) mu = 2 * (spnh[q] - ptop) / tdp[q];
-        else mu = (spnh[q] - spnh[q - 16]) / ((tdp[q] + tdp[q - 16]) / 2);
+        if (k == 0) mu = div_fast(2 * (spnh[q] - ptop), tdp[q]);
+        else mu = div_fast(spnh[q] - spnh[q - 16], (tdp[q] + tdp[q - 16]) / 2);
         w0[j] = w0[j] + dt3 * g * (mu - 1);
         const double gwh = (k == 0) ? 0.0 : gwphis_at(tv, tdp, k, p, gp1, gp2);
         phi0[j] = phi0[j] + dt3 * g * tw[q] - dt3 * gwh;
@@ -897,7 +897,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
       }
     }
     xmax = block_max(xmax, red, tid);
-    deltaerr = xmax / wmax;                                                         // IM:330
+    deltaerr = div_fast(xmax, wmax);                                                         // IM:330
     itercount++;
     if (deltaerr < 1.0e-11) break;                                                  // IM:335
 #pragma unroll
@@ -1072,7 +1072,7 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace1_kernel(const HvArgs A)
     const bool act = kk < nlev;
     const int k = act ? kk : nlev - 1, q = k * 16 + p;
     const double dp = A.st.dp[em + q];
-    const double theta = A.th_is_theta ? A.st.th[em + q] : A.st.th[em + q] / dp;     // PA:615-621
+    const double theta = A.th_is_theta ? A.st.th[em + q] : div_fast(A.st.th[em + q], dp);   // PA:615-621
     double s[4], lap[4], l1, l2;
     s[0] = dp - A.ref.dp_ref[em + q];
     s[1] = theta - A.ref.theta_ref[em + q];
@@ -1154,7 +1154,7 @@ __global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A
     const double tv1 = dt * dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2) * rs;
     const double tv2 = dt * dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2) * rs;
     const double dp_old = A.st.dp[em + q];
-    const double theta_old = A.th_is_theta ? A.st.th[em + q] : A.st.th[em + q] / dp_old;
+    const double theta_old = A.th_is_theta ? A.st.th[em + q] : div_fast(A.st.th[em + q], dp_old);
     // remove/add reference state exactly as PA:629-647 does (rounding of (x-r)+r)
     const double dref = A.ref.dp_ref[em + q], tref = A.ref.theta_ref[em + q], pref = A.ref.phi_ref[ei + q];
     const double dp_new = ((dp_old - dref) + dref) + tdp;

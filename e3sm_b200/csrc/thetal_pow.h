@@ -47,7 +47,9 @@ THETAL_HD double u2d(uint64_t u)
 THETAL_HD double rcp46(double d)
 {
 #if defined(__CUDA_ARCH__)
-  double r = (double)__frcp_rn((float)d);
+  float rf;                                        // one MUFU.RCP (2^-23); __frcp_rn would add a range
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rf) : "f"((float)d));   // check, a branch and a slow path
+  double r = (double)rf;
 #else
   double r = (double)(1.0f / (float)d);
 #endif
