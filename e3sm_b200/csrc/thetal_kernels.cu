@@ -522,7 +522,7 @@ void launch_caar_dss_post(const DssArgs &A, cudaStream_t st)
 constexpr int DIRK_THREADS = 256;
 constexpr int DIRK_ARRAYS = 6;
 #ifndef DIRK_MINB
-#define DIRK_MINB 4
+#define DIRK_MINB 3
 #endif
 
 __host__ __device__ inline size_t dirk_smem_bytes(int nlev)
