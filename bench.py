@@ -148,7 +148,8 @@ def run_reference(args, world, rank, td):
     if rank != 0:
         return
     p = config(args.config)
-    val, cores, sample, sec = cpu_reference_sample(p, warmup=max(1, min(args.warmup, 2)), steps=args.steps)
+    # each bench "step" of this arm is a bounded sample: 20 dynamics steps of the 384-element sphere
+    val, cores, sample, sec = cpu_reference_sample(p, warmup=max(1, min(args.warmup, 2)), steps=20 * args.steps)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3 * p.nelem / 384.0,

@@ -163,6 +163,9 @@ __host__ __device__ inline size_t caar_smem_bytes(int nlev)
   return sizeof(double) * 16 * (7 * (size_t)nlev + 2 * nlevp + (CAAR_THREADS / 16) * CAAR_SLOTS);
 }
 
+// FORM = theta_advect_form, PGRAD = pgrad_correction, ACCUM = (eta_ave_w != 0): compile-time so that the
+// level loop is one straight-line block the scheduler can interleave freely
+template <int FORM, bool PGRAD, bool ACCUM>
 __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArgs A)
 {
   extern __shared__ double smem[];
@@ -230,7 +233,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   const double fcor = A.geo.fcor[(size_t)ie * 16 + p], spheremp = A.geo.spheremp[(size_t)ie * 16 + p];
   const double gps1 = A.geo.gradphis[(size_t)ie * 32 + p], gps2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
   const double s1 = A.scale1, s2 = A.scale2, s3 = A.scale3, dt2 = A.dt2;
-  const bool accum = (A.eta_ave_w != 0.0);
+  constexpr bool accum = ACCUM;
   const int niter = (nlev + KS - 1) / KS;
 
   for (int it = 0; it < niter; it++) {
@@ -268,13 +271,13 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     div_prep(t, v1 * dp, v2 * dp, gv1, gv2);                                        // PA:1188-1192
     vort_prep(t, v1, v2, vc1, vc2);
     scr[0 * 16 + p] = gv1; scr[1 * 16 + p] = gv2; scr[2 * 16 + p] = vc1; scr[3 * 16 + p] = vc2;
-    if (A.prm.theta_advect_form != 1) {
+    if (FORM != 1) {
       div_prep(t, v1 * th, v2 * th, gt1, gt2);                                      // PA:1373-1375
       scr[4 * 16 + p] = gt1; scr[5 * 16 + p] = gt2;
     }
     scr[6 * 16 + p] = (wk * wk + wk1 * wk1) / 4;                                    // PA:1401
     scr[7 * 16 + p] = (v1 * v1 + v2 * v2) / 2;                                      // PA:1409
-    if (A.prm.theta_advect_form != 0) { scr[8 * 16 + p] = theta; scr[9 * 16 + p] = theta * exner; }
+    if (FORM != 0) { scr[8 * 16 + p] = theta; scr[9 * 16 + p] = theta * exner; }
     __syncwarp();
 
     const double divdp = div_finish(t, scr, scr + 16);
@@ -291,13 +294,13 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
 
     // theta tendency PA:1372-1398
     double div_v_theta;
-    if (A.prm.theta_advect_form == 0) {
+    if (FORM == 0) {
       div_v_theta = div_finish(t, scr + 64, scr + 80);
     } else {
       double gth1, gth2;
       gradient_sphere(t, scr + 8 * 16, gth1, gth2);
       const double nc = theta * divdp + dp * v1 * gth1 + dp * v2 * gth2;
-      if (A.prm.theta_advect_form == 1) div_v_theta = nc;
+      if (FORM == 1) div_v_theta = nc;
       else div_v_theta = div_finish(t, scr + 64, scr + 80) / 2 + nc / 2;
     }
     const double theta_tens = (-div_v_theta) * s1;                                  // theta_vadv = 0 (rsplit>0)
@@ -313,7 +316,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     wv1 = wv1 - (wk * gw1_k + wk1 * gw1_k1) / 2;
     wv2 = wv2 - (wk * gw2_k + wk1 * gw2_k1) / 2;
     double gp1 = CP * theta * ge1, gp2 = CP * theta * ge2;
-    if (A.prm.theta_advect_form == 2) {                                             // PA:1446-1452
+    if (FORM == 2) {                                             // PA:1446-1452
       double gte1, gte2, gth1, gth2;
       gradient_sphere(t, scr + 9 * 16, gte1, gte2);
       gradient_sphere(t, scr + 8 * 16, gth1, gth2);
@@ -322,7 +325,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     }
     double mg1 = (mu_k * gphi1_k + mu_k1 * gphi1_k1) / 2;                           // PA:1455-1458
     double mg2 = (mu_k * gphi2_k + mu_k1 * gphi2_k1) / 2;
-    if (A.prm.pgrad_correction == 1) {                                              // PA:1460-1477
+    if (PGRAD) {                                              // PA:1460-1477
       __syncwarp();
       scr[0 * 16 + p] = log(exner);
       __syncwarp();
@@ -385,15 +388,33 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   }
 }
 
-void launch_caar_pre(const CaarArgs &A, cudaStream_t st)
+template <int FORM, bool PGRAD, bool ACCUM>
+static void launch_caar_pre_t(const CaarArgs &A, cudaStream_t st)
 {
   const size_t sm = caar_smem_bytes(A.prm.nlev);
   static size_t configured = 0;
   if (sm > configured) {
-    cudaFuncSetAttribute(caar_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaFuncSetAttribute(caar_pre_kernel<FORM, PGRAD, ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     configured = sm;
   }
-  caar_pre_kernel<<<A.prm.nelem, CAAR_THREADS, sm, st>>>(A);
+  caar_pre_kernel<FORM, PGRAD, ACCUM><<<A.prm.nelem, CAAR_THREADS, sm, st>>>(A);
+}
+
+template <int FORM, bool PGRAD>
+static void launch_caar_pre_a(const CaarArgs &A, cudaStream_t st)
+{
+  if (A.eta_ave_w != 0.0) launch_caar_pre_t<FORM, PGRAD, true>(A, st);
+  else launch_caar_pre_t<FORM, PGRAD, false>(A, st);
+}
+
+void launch_caar_pre(const CaarArgs &A, cudaStream_t st)
+{
+  const bool pg = A.prm.pgrad_correction == 1;
+  switch (A.prm.theta_advect_form) {
+    case 0: pg ? launch_caar_pre_a<0, true>(A, st) : launch_caar_pre_a<0, false>(A, st); break;
+    case 1: pg ? launch_caar_pre_a<1, true>(A, st) : launch_caar_pre_a<1, false>(A, st); break;
+    default: pg ? launch_caar_pre_a<2, true>(A, st) : launch_caar_pre_a<2, false>(A, st); break;
+  }
 }
 
 // ==========================================================================================
