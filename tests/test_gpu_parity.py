@@ -130,6 +130,33 @@ def test_ten_steps(case_c1):
     d.close()
 
 
+@pytest.mark.parametrize("cfg,over", [("C2", {}), ("C5", {}), ("C4", {}), ("C3", {}), ("C2", {"tstep_type": 10}),
+                                      ("C2", {"tstep_type": 7, "theta_advect_form": 2, "pgrad_correction": 1})])
+def test_steps_at_full_vertical_resolution(cfg, over):
+    """The bench/scaling configurations at their real nlev (72 / 128 levels, their dt, hyperviscosity
+    and sponge settings) on the coarse ne4 sphere: three steps from the JW state, GPU vs oracle."""
+    from e3sm_b200.dycore import build_case
+    from e3sm_b200.params import config
+    p = config(cfg).with_(ne=4, **over)
+    grid, hv, st, phis, gradphis, refs = build_case(p)
+    case = (p, grid, hv, st, phis, gradphis, refs)
+    p, o, so, d = make_pair(case, st.copy())
+    nm1, n0, np1 = 0, 1, 2
+    for _ in range(3):
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        d.prim_advance_exp(p.tstep, nm1, n0, np1)
+        nm1, n0, np1 = n0, np1, nm1
+    assert o.error_flag == 0
+    sg = d.get_state()
+    for f in ("v", "vtheta_dp", "phinh_i", "dp3d"):
+        r = rel_l2(getattr(sg, f)[:, n0], getattr(so, f)[:, n0])
+        assert r <= TOL, (cfg, over, f, r)
+    # w starts from rest: measure it against its own max with an absolute floor
+    dw = float(np.abs(sg.w_i[:, n0] - so.w_i[:, n0]).max())
+    assert dw <= 1e-9 * max(1.0, float(np.abs(so.w_i[:, n0]).max())), dw
+    d.close()
+
+
 def test_ten_day_baroclinic_wave_diagnostics(case_c1):
     """North-star check: 10 simulated days of the JW baroclinic wave (C1: ne4 L26, dt=600 s, 1440
     dynamics steps, tstep_type 9 + hyperviscosity + sponge); min surface pressure, dry mass and total
