@@ -171,6 +171,8 @@ def run_ours(args, world, rank, local, td):
     from e3sm_b200.initial import State
     from e3sm_b200.partition import Partition
     p = config(args.config)
+    if args.weak_ne:
+        p = p.with_(ne=args.weak_ne)
     part, nccl_id = None, None
     if world > 1:   # elements cut along HOMME's space-filling curve, one slice per GPU, DSS halos over NCCL
         part = Partition(p.ne, world)
@@ -266,10 +268,12 @@ def run_ours(args, world, rank, local, td):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
+            "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "weak" if (world == 1 or args.weak_ne) else "strong",
             "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.config}: theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem_total} elements"
+            "config": {"workload": f"{args.config}{' (weak scaling: ne = 30*sqrt(N), ~5400 elements per GPU)' if args.weak_ne else ''}"
+                                   f": theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem_total} elements"
                                    f", tstep_type {p.tstep_type}, dt={p.tstep:g}s, hypervis_subcycle {p.hypervis_subcycle}, sponge on",
                        "l2": "inputs larger than L2 (every kernel streams >= 300 MB of state; L2 is 126 MB)",
                        "parallelism": "1 rank per GPU" + ("" if world == 1 else
@@ -296,12 +300,18 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default=None, help="C1..C5; default C2 on 1 GPU, C3 (ne120, partitioned) on N>1")
+    ap.add_argument("--config", default=None,
+                    help="C1..C5; default C2. On N>1 GPUs the default is C2 weak-scaled (ne = round(30*sqrt(N)), "
+                         "the same work per element and ~5400 elements per GPU, partitioned along the space-filling "
+                         "curve); pass --config C3 for the ne120 strong-scaling case")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     world, rank, local, td = dist_setup(args.gpus)
+    args.weak_ne = 0
     if args.config is None:
-        args.config = "C2" if world == 1 else "C3"
+        args.config = "C2"
+        if world > 1:
+            args.weak_ne = int(round(30.0 * world ** 0.5))      # 2: ne42, 4: ne60, 8: ne85
     if args.impl == "reference":
         if args.steps > 5:
             args.steps = 5          # bounded sample: each step is ~1-4 s of CPU work

@@ -54,6 +54,13 @@ struct Session {
   ncclUniqueId nccl_id{};
   bool have_id = false;
   long halo_bytes = 0, exchanges = 0;
+  // overlap of the exchange with the DSS-consuming kernel: elements without a ghost neighbour
+  // (interior) are consumed while the halo is in flight on stream2, the others after it landed
+  std::vector<int> h_interior, h_boundary;
+  int *d_interior = nullptr, *d_boundary = nullptr;
+  cudaStream_t stream2 = nullptr;
+  cudaEvent_t ev_prod = nullptr, ev_halo = nullptr;
+  int overlap = 1;
   // device
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -134,6 +141,10 @@ void initialize_hommexx_session(void)
   CUDA_OK(cudaEventCreate(&S.ev0));
   CUDA_OK(cudaEventCreate(&S.ev1));
   if (S.nranks > 1) {
+    CUDA_OK(cudaStreamCreateWithFlags(&S.stream2, cudaStreamNonBlocking));
+    CUDA_OK(cudaEventCreateWithFlags(&S.ev_prod, cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&S.ev_halo, cudaEventDisableTiming));
+    if (getenv("THETAL_B200_NO_OVERLAP")) S.overlap = 0;      // A/B switch
     if (!S.have_id) { fail(4, "nranks > 1 needs the ncclUniqueId of rank 0 (thetal_b200_init_comm)"); return; }
     ncclResult_t r = ncclCommInitRank(&S.comm, S.nranks, S.nccl_id, S.rank);
     if (r != ncclSuccess) { fail(5, std::string("ncclCommInitRank: ") + ncclGetErrorString(r)); return; }
@@ -151,6 +162,9 @@ void finalize_hommexx_session(void)
   if (S.ev0) cudaEventDestroy(S.ev0);
   if (S.ev1) cudaEventDestroy(S.ev1);
   if (S.stream) cudaStreamDestroy(S.stream);
+  if (S.stream2) cudaStreamDestroy(S.stream2);
+  if (S.ev_prod) cudaEventDestroy(S.ev_prod);
+  if (S.ev_halo) cudaEventDestroy(S.ev_halo);
   const int dev = S.device, rank = S.rank, nranks = S.nranks, aoe = S.abort_on_error;
   const bool have_id = S.have_id;
   const ncclUniqueId id = S.nccl_id;
@@ -291,6 +305,12 @@ void finalize_connectivity(void)
       for (int j = 0; j < 5; j++)
         if (k[order[j]] >= 0) { require(n < 3, "more than 3 DSS neighbours at a point"); S.hdss[((size_t)e * 16 + p) * 3 + n++] = k[order[j]]; }
     }
+  S.h_interior.clear(); S.h_boundary.clear();
+  for (int e = 0; e < nelem; e++) {
+    bool ghost_nbr = false;
+    for (int j = 0; j < 48; j++) if (S.hdss[(size_t)e * 48 + j] >= nelem * 16) ghost_nbr = true;
+    (ghost_nbr ? S.h_boundary : S.h_interior).push_back(e);
+  }
 }
 
 }  // extern "C"
@@ -451,6 +471,10 @@ void init_functors_c(const int *allocate_buffer)
     CUDA_OK(cudaMemcpy(S.d_recv_idx, S.hrecv_idx.data(), S.hrecv_idx.size() * sizeof(int), cudaMemcpyHostToDevice));
     S.d_sendbuf = dalloc<double>(S.hsend_idx.size() * nlyr);
     S.d_recvbuf = dalloc<double>(S.hrecv_idx.size() * nlyr);
+    S.d_interior = dalloc<int>(S.h_interior.size() + 1);
+    S.d_boundary = dalloc<int>(S.h_boundary.size() + 1);
+    CUDA_OK(cudaMemcpy(S.d_interior, S.h_interior.data(), S.h_interior.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMemcpy(S.d_boundary, S.h_boundary.data(), S.h_boundary.size() * sizeof(int), cudaMemcpyHostToDevice));
   }
   S.der.vn0 = dalloc<double>((size_t)n * 32 * nlev);
   S.der.eta_dot_dpdn = dalloc<double>((size_t)n * 16 * (nlev + 1));
@@ -517,21 +541,37 @@ struct ProfScope {   // per-family device time when thetal_b200_profile_step is 
 // nk levels of each field (+ w_i(nlevp) when wbot); all on S.stream, so it is ordered between the
 // kernel that produced `t` and the DSS kernel that gathers from it.
 #define NCCL_OK(x) do { ncclResult_t r_ = (x); if (r_ != ncclSuccess) { fail(5, std::string(#x) + ": " + ncclGetErrorString(r_)); } } while (0)
-void halo_exchange(const StatePtrs &t, int nk, int wbot)
+void halo_exchange(const StatePtrs &t, int nk, int wbot, cudaStream_t st)
 {
   if (S.peers.empty()) return;
   const int nlev = S.nlev, nlyr = 6 * nk + wbot;
-  launch_halo_pack(t, S.d_send_idx, (int)S.hsend_idx.size(), nk, wbot, nlev, S.d_sendbuf, S.stream);
+  launch_halo_pack(t, S.d_send_idx, (int)S.hsend_idx.size(), nk, wbot, nlev, S.d_sendbuf, st);
   NCCL_OK(ncclGroupStart());
   for (const Peer &p : S.peers) {
-    NCCL_OK(ncclSend(S.d_sendbuf + (size_t)p.send_off * nlyr, (size_t)p.send_cnt * nlyr, ncclDouble, p.rank, S.comm, S.stream));
-    NCCL_OK(ncclRecv(S.d_recvbuf + (size_t)p.recv_off * nlyr, (size_t)p.recv_cnt * nlyr, ncclDouble, p.rank, S.comm, S.stream));
+    NCCL_OK(ncclSend(S.d_sendbuf + (size_t)p.send_off * nlyr, (size_t)p.send_cnt * nlyr, ncclDouble, p.rank, S.comm, st));
+    NCCL_OK(ncclRecv(S.d_recvbuf + (size_t)p.recv_off * nlyr, (size_t)p.recv_cnt * nlyr, ncclDouble, p.rank, S.comm, st));
   }
   NCCL_OK(ncclGroupEnd());
-  launch_halo_unpack(t, S.d_recv_idx, (int)S.hrecv_idx.size(), nk, wbot, nlev, S.d_recvbuf, S.stream);
+  launch_halo_unpack(t, S.d_recv_idx, (int)S.hrecv_idx.size(), nk, wbot, nlev, S.d_recvbuf, st);
   S.launches += 2;
   S.exchanges += 1;
   S.halo_bytes += (long)(S.hsend_idx.size() + S.hrecv_idx.size()) * nlyr * 8;
+}
+
+// One DSS across ranks: `consume(elist, count)` launches the kernel that gathers from `t` (on S.stream)
+// for the listed elements (null = all).  The halo of `t` travels on stream2 while the elements with
+// no ghost neighbour are consumed; the partition-boundary elements follow once it has been unpacked.
+template <class F> void exchange_and_consume(const StatePtrs &t, int nk, int wbot, F consume)
+{
+  if (S.peers.empty()) { consume(nullptr, 0); return; }
+  if (!S.overlap) { halo_exchange(t, nk, wbot, S.stream); consume(nullptr, 0); return; }
+  CUDA_OK(cudaEventRecord(S.ev_prod, S.stream));
+  CUDA_OK(cudaStreamWaitEvent(S.stream2, S.ev_prod, 0));
+  halo_exchange(t, nk, wbot, S.stream2);
+  CUDA_OK(cudaEventRecord(S.ev_halo, S.stream2));
+  consume(S.d_interior, (int)S.h_interior.size());
+  CUDA_OK(cudaStreamWaitEvent(S.stream, S.ev_halo, 0));
+  consume(S.d_boundary, (int)S.h_boundary.size());
 }
 
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
@@ -541,12 +581,15 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
   a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
   a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
   { ProfScope ps(0); launch_caar_pre(a, S.stream); }
-  { ProfScope ps(5); halo_exchange(S.tensA, S.nlev, 1); }
   DssArgs d;
   d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
   d.do_limiter = (s3 != 0.0);
-  { ProfScope ps(1); launch_caar_dss_post(d, S.stream); }
-  S.launches += 2;
+  {
+    ProfScope ps(1);
+    exchange_and_consume(S.tensA, S.nlev, 1, [&](const int *el, int n) {
+      d.elist = el; d.ecount = n; launch_caar_dss_post(d, S.stream); S.launches += 1; });
+  }
+  S.launches += 1;
 }
 
 void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
@@ -571,11 +614,13 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
   for (int ic = 0; ic < hvs; ic++) {
     a.dt = dt2 / hvs;
     a.th_is_theta = ic > 0; a.last_subcycle = (ic == hvs - 1);
+    a.elist = nullptr; a.ecount = 0;
     a.nu_ratio = nu_ratio1; a.tin = S.tensB; a.tout = S.tensA; launch_hv(0, a, S.stream);
-    halo_exchange(S.tensA, S.nlev, 0);
-    a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB; launch_hv(1, a, S.stream);
-    halo_exchange(S.tensB, S.nlev, 0);
-    a.tin = S.tensB; a.tout = S.tensA; launch_hv(2, a, S.stream);
+    a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB;
+    exchange_and_consume(S.tensA, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(1, a, S.stream); });
+    a.tin = S.tensB; a.tout = S.tensA;
+    exchange_and_consume(S.tensB, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(2, a, S.stream); });
+    a.elist = nullptr; a.ecount = 0;
     S.launches += 3;
   }
   if (hvs == 0) fail(3, "hypervis_subcycle must be >= 1");
@@ -583,9 +628,11 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
     const int nt_ = S.prm.hypervis_subcycle_tom;
     for (int ic = 0; ic < nt_; ic++) {
       a.dt = dt2 / nt_; a.th_is_theta = 0; a.last_subcycle = 0;
+      a.elist = nullptr; a.ecount = 0;
       a.tin = S.tensB; a.tout = S.tensA; launch_hv(3, a, S.stream);
-      halo_exchange(S.tensA, S.prm.nlev_tom, 0);
-      a.tin = S.tensA; a.tout = S.tensB; launch_hv(4, a, S.stream);
+      a.tin = S.tensA; a.tout = S.tensB;
+      exchange_and_consume(S.tensA, S.prm.nlev_tom, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(4, a, S.stream); });
+      a.elist = nullptr; a.ecount = 0;
       S.launches += 2;
     }
   }

@@ -468,7 +468,8 @@ constexpr int DSS_THREADS = 256;
 __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const DssArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
-  const int ie = blockIdx.x, tid = threadIdx.x, p = tid & 15, kslot = tid >> 4;
+  const int ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x;
+  const int tid = threadIdx.x, p = tid & 15, kslot = tid >> 4;
   constexpr int KS = DSS_THREADS / 16;
   const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
   const int s0 = src[0], s1 = src[1], s2 = src[2];
@@ -531,7 +532,8 @@ __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const Dss
 
 void launch_caar_dss_post(const DssArgs &A, cudaStream_t st)
 {
-  caar_dss_post_kernel<<<A.prm.nelem, DSS_THREADS, 0, st>>>(A);
+  const int nb = A.elist ? A.ecount : A.prm.nelem;
+  if (nb > 0) caar_dss_post_kernel<<<nb, DSS_THREADS, 0, st>>>(A);
 }
 
 // ==========================================================================================
@@ -1065,7 +1067,7 @@ __device__ __forceinline__ void laplace_level(const Pt &t, const PtW &w, double 
 __host__ __device__ inline size_t hv_smem_bytes() { return sizeof(double) * (HV_THREADS / 16) * HV_SLOTS * 16; }
 
 // pass 1 (PA:629-636 + VT:93-107): laplacians of (state - reference state) -> tout
-__global__ void __launch_bounds__(HV_THREADS) hv_laplace1_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace1_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
@@ -1088,18 +1090,30 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace1_kernel(const HvArgs A)
     if (tid == 7) prefetch_l2(A.ref.phi_ref + ei, bi);
   }
   const int niter = (nlev + KS - 1) / KS;
+  // software pipeline: the nine input values of the next level are requested before the laplacians of
+  // the current one are computed
+  double n_dp, n_th, n_w, n_phi, n_v1, n_v2, n_rdp, n_rth, n_rphi;
+  auto fetch = [&](int it_) {
+    const int kk_ = it_ * KS + kslot;
+    const int k_ = kk_ < nlev ? kk_ : nlev - 1, q_ = k_ * 16 + p;
+    n_dp = A.st.dp[em + q_]; n_th = A.st.th[em + q_]; n_w = A.st.w[ei + q_]; n_phi = A.st.phi[ei + q_];
+    n_v1 = A.st.v[ev + k_ * 32 + p]; n_v2 = A.st.v[ev + k_ * 32 + 16 + p];
+    n_rdp = A.ref.dp_ref[em + q_]; n_rth = A.ref.theta_ref[em + q_]; n_rphi = A.ref.phi_ref[ei + q_];
+  };
+  fetch(0);
   for (int it = 0; it < niter; it++) {
     const int kk = it * KS + kslot;
     const bool act = kk < nlev;
     const int k = act ? kk : nlev - 1, q = k * 16 + p;
-    const double dp = A.st.dp[em + q];
-    const double theta = A.th_is_theta ? A.st.th[em + q] : div_fast(A.st.th[em + q], dp);   // PA:615-621
+    const double dp = n_dp, thv = n_th, wv = n_w, phiv = n_phi, v1 = n_v1, v2 = n_v2;
+    const double rdp = n_rdp, rth = n_rth, rphi = n_rphi;
+    if (it + 1 < niter) fetch(it + 1);
+    const double theta = A.th_is_theta ? thv : div_fast(thv, dp);                    // PA:615-621
     double s[4], lap[4], l1, l2;
-    s[0] = dp - A.ref.dp_ref[em + q];
-    s[1] = theta - A.ref.theta_ref[em + q];
-    s[2] = A.st.w[ei + q];
-    s[3] = A.st.phi[ei + q] - A.ref.phi_ref[ei + q];
-    const double v1 = A.st.v[ev + k * 32 + p], v2 = A.st.v[ev + k * 32 + 16 + p];
+    s[0] = dp - rdp;
+    s[1] = theta - rth;
+    s[2] = wv;
+    s[3] = phiv - rphi;
     laplace_level(t, w, scr, A.nu_ratio, s, v1, v2, lap, l1, l2);
     if (act) {
       A.tout.dp[em + q] = lap[0]; A.tout.th[em + q] = lap[1];
@@ -1110,10 +1124,10 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace1_kernel(const HvArgs A)
 }
 
 // pass 2 (VT:134-164 + PA:657-663): DSS(tin) * rspheremp -> laplacian again -> * (-nu) -> tout
-__global__ void __launch_bounds__(HV_THREADS) hv_laplace2_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace2_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
   double *scr = smem + kslot * (HV_SLOTS * 16);
@@ -1133,18 +1147,28 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace2_kernel(const HvArgs A)
     if (tid == 4) prefetch_l2(A.tin.phi + ei, (unsigned)(si * 8));
   }
   const int niter = (nlev + KS - 1) / KS;
+  double n_s[6];
+  auto gather = [&](int it_) {
+    const int kk_ = it_ * KS + kslot;
+    const int k_ = kk_ < nlev ? kk_ : nlev - 1, q_ = k_ * 16 + p;
+    const size_t om = (size_t)k_ * 16, ov_ = (size_t)k_ * 32;
+    n_s[0] = rs * dss_sum(A.tin.dp, sm_, om, A.tin.dp[em + q_], s0, s1, s2);
+    n_s[1] = rs * dss_sum(A.tin.th, sm_, om, A.tin.th[em + q_], s0, s1, s2);
+    n_s[2] = rs * dss_sum(A.tin.w, si, om, A.tin.w[ei + q_], s0, s1, s2);
+    n_s[3] = rs * dss_sum(A.tin.phi, si, om, A.tin.phi[ei + q_], s0, s1, s2);
+    n_s[4] = rs * dss_sum(A.tin.v, sv, ov_, A.tin.v[ev + ov_ + p], s0, s1, s2);
+    n_s[5] = rs * dss_sum(A.tin.v, sv, ov_ + 16, A.tin.v[ev + ov_ + 16 + p], s0, s1, s2);
+  };
+  gather(0);
   for (int it = 0; it < niter; it++) {
     const int kk = it * KS + kslot;
     const bool act = kk < nlev;
     const int k = act ? kk : nlev - 1, q = k * 16 + p;
-    const size_t om = (size_t)k * 16, ov = (size_t)k * 32;
+    const size_t ov = (size_t)k * 32;
     double s[4], lap[4], l1, l2;
-    s[0] = rs * dss_sum(A.tin.dp, sm_, om, A.tin.dp[em + q], s0, s1, s2);
-    s[1] = rs * dss_sum(A.tin.th, sm_, om, A.tin.th[em + q], s0, s1, s2);
-    s[2] = rs * dss_sum(A.tin.w, si, om, A.tin.w[ei + q], s0, s1, s2);
-    s[3] = rs * dss_sum(A.tin.phi, si, om, A.tin.phi[ei + q], s0, s1, s2);
-    const double v1 = rs * dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2);
-    const double v2 = rs * dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2);
+    s[0] = n_s[0]; s[1] = n_s[1]; s[2] = n_s[2]; s[3] = n_s[3];
+    const double v1 = n_s[4], v2 = n_s[5];
+    if (it + 1 < niter) gather(it + 1);        // next level's DSS sums are requested before this level's laplacians
     laplace_level(t, w, scr, A.nu_ratio, s, v1, v2, lap, l1, l2);
     if (act) {
       A.tout.dp[em + q] = -A.prm.nu_p * lap[0]; A.tout.th[em + q] = -A.prm.nu * lap[1];
@@ -1157,7 +1181,7 @@ __global__ void __launch_bounds__(HV_THREADS) hv_laplace2_kernel(const HvArgs A)
 // pass 3 (PA:674-758, 767-774): DSS(tin) * dt * rspheremp added to the state
 __global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A)
 {
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
   const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
@@ -1194,7 +1218,7 @@ __global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A
 }
 
 // sponge pass A (PA:784-800): xfac * laplacian of the top nlev_tom levels of the state -> tout
-__global__ void __launch_bounds__(HV_THREADS) hv_sponge_laplace_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, 2) hv_sponge_laplace_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = blockIdx.x, tid = threadIdx.x;
@@ -1226,7 +1250,7 @@ __global__ void __launch_bounds__(HV_THREADS) hv_sponge_laplace_kernel(const HvA
 // sponge pass B (PA:820-852): state += DSS(tin) * rspheremp on the top nlev_tom levels
 __global__ void __launch_bounds__(HV_THREADS) hv_sponge_update_kernel(const HvArgs A)
 {
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
   const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
@@ -1249,12 +1273,14 @@ __global__ void __launch_bounds__(HV_THREADS) hv_sponge_update_kernel(const HvAr
 void launch_hv(int which, const HvArgs &A, cudaStream_t st)
 {
   const size_t sm = hv_smem_bytes();
+  const int nb = A.elist ? A.ecount : A.prm.nelem;     // element lists only for the DSS consumers 1, 2, 4
+  if (nb <= 0) return;
   switch (which) {
     case 0: hv_laplace1_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
-    case 1: hv_laplace2_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
-    case 2: hv_update_kernel<<<A.prm.nelem, HV_THREADS, 0, st>>>(A); break;
+    case 1: hv_laplace2_kernel<<<nb, HV_THREADS, sm, st>>>(A); break;
+    case 2: hv_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
     case 3: hv_sponge_laplace_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
-    case 4: hv_sponge_update_kernel<<<A.prm.nelem, HV_THREADS, 0, st>>>(A); break;
+    case 4: hv_sponge_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
   }
 }
 

@@ -20,6 +20,8 @@ struct DssArgs {
   Params prm;
   double dt2, scale1, scale3;
   int do_limiter;
+  const int *elist;         // optional element list (interior / partition-boundary pass); null = all
+  int ecount;
 };
 
 struct DirkArgs {
@@ -41,6 +43,8 @@ struct HvArgs {
   double dt, nu_ratio;
   int th_is_theta;          // st.th currently holds theta (not vtheta_dp)
   int last_subcycle;        // convert back to vtheta_dp and reset w b.c. (PA:767-774)
+  const int *elist;         // optional element list for the DSS-consuming kernels; null = all
+  int ecount;
 };
 
 struct ComboArgs {
