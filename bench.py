@@ -176,7 +176,8 @@ def run_ours(args, world, rank, local, td):
         # unchanged -- dt ~ 1/ne, nu ~ (30/ne)^3.2 (rule quoted in the reference's thetanh namelists)
         f = 30.0 / args.weak_ne
         p = p.with_(ne=args.weak_ne, tstep=p.tstep * f, nu=p.nu * f ** 3.2, nu_p=p.nu_p * f ** 3.2,
-                    nu_s=p.nu_s * f ** 3.2, nu_div=p.nu_div * f ** 3.2)
+                    nu_s=p.nu_s * f ** 3.2, nu_div=p.nu_div * f ** 3.2,
+                    nu_top=p.nu_top * f)      # explicit sponge: nu_top * dt * ne^2 held fixed
     part, nccl_id = None, None
     if world > 1:   # elements cut along HOMME's space-filling curve, one slice per GPU, DSS halos over NCCL
         part = Partition(p.ne, world)

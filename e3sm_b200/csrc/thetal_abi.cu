@@ -60,7 +60,7 @@ struct Session {
   int *d_interior = nullptr, *d_boundary = nullptr;
   cudaStream_t stream2 = nullptr;
   cudaEvent_t ev_prod = nullptr, ev_halo = nullptr;
-  int overlap = 1;
+  int overlap = 0;          // measured on 2 and 8 B200: the split launches cost more than the hidden exchange saves
   // device
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -144,7 +144,7 @@ void initialize_hommexx_session(void)
     CUDA_OK(cudaStreamCreateWithFlags(&S.stream2, cudaStreamNonBlocking));
     CUDA_OK(cudaEventCreateWithFlags(&S.ev_prod, cudaEventDisableTiming));
     CUDA_OK(cudaEventCreateWithFlags(&S.ev_halo, cudaEventDisableTiming));
-    if (getenv("THETAL_B200_NO_OVERLAP")) S.overlap = 0;      // A/B switch
+    if (getenv("THETAL_B200_OVERLAP")) S.overlap = 1;         // A/B switch (off by default)
     if (!S.have_id) { fail(4, "nranks > 1 needs the ncclUniqueId of rank 0 (thetal_b200_init_comm)"); return; }
     ncclResult_t r = ncclCommInitRank(&S.comm, S.nranks, S.nccl_id, S.rank);
     if (r != ncclSuccess) { fail(5, std::string("ncclCommInitRank: ") + ncclGetErrorString(r)); return; }
