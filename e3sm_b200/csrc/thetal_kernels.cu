@@ -476,6 +476,13 @@ __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const Dss
   const double rs = A.geo.rspheremp[(size_t)ie * 16 + p];
   const size_t ev = 32 * (size_t)nlev, em = 16 * (size_t)nlev, ei = 16 * (size_t)nlevp;
   int lim_dp = 0, lim_th = 0;
+  if (tid < 5) {      // own pre-DSS columns towards L2 (the neighbours' CTAs do the same for theirs)
+    if (tid == 0) prefetch_l2(A.tens.v + ie * ev, (unsigned)(ev * 8));
+    if (tid == 1) prefetch_l2(A.tens.dp + ie * em, (unsigned)(em * 8));
+    if (tid == 2) prefetch_l2(A.tens.th + ie * em, (unsigned)(em * 8));
+    if (tid == 3) prefetch_l2(A.tens.w + ie * ei, (unsigned)(ei * 8));
+    if (tid == 4) prefetch_l2(A.tens.phi + ie * ei, (unsigned)(ei * 8));
+  }
 
   for (int k = kslot; k < nlev; k += KS) {
     const size_t ov = (size_t)k * 32, om = (size_t)k * 16;

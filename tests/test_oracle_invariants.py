@@ -160,3 +160,22 @@ def test_oracle_time_level_aliasing(case_c1, parity_state_c1, tt):
     ob.prim_advance_exp(dt, 2, 0, 1)
     for f in a.FIELDS:
         assert np.array_equal(getattr(a, f)[:, 2], getattr(b, f)[:, 1]), f   # also thread-count independent
+
+
+def test_cfl_report_matches_print_cfl_formulas():
+    """e3sm_b200/cfl.py against hand-evaluated global_norms_mod.F90:339-387 numbers on ne30."""
+    from e3sm_b200.cfl import cfl_report, hypervis_is_stable, max_norm_dinv
+    from e3sm_b200.geometry import CubedSphere
+    from e3sm_b200.params import config
+    g = CubedSphere(30)
+    nd = max_norm_dinv(g)
+    # equiangular cube: the element at the face centre has Dinv = (4 ne / pi) I, corners are ~1.5x that
+    assert 4 * 30 / np.pi < nd < 1.6 * 4 * 30 / np.pi
+    p = config("C2")
+    r = cfl_report(g, p)
+    x = nd / g.rearth
+    assert np.isclose(r["nu_vor_dt"], 1.0 / (p.nu * 144.0 * x ** 4))
+    assert np.isclose(r["nu_top_dt"], 1.0 / (4 * p.nu_top * 12.0 * x ** 2))
+    assert np.isclose(r["gravity_wave_dt"], 1.0 / (342.0 * x * 1.5))
+    assert hypervis_is_stable(g, p) and hypervis_is_stable(g, config("C5"))
+    assert not hypervis_is_stable(g, p.with_(nu=1e16, nu_div=1e16))
