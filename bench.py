@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from e3sm_b200.params import bytes_per_element_step, config  # noqa: E402
+from e3sm_b200.params import bytes_per_element_step, config, weak_scaled  # noqa: E402
 
 METRIC = "theta-l dycore element-steps/s"
 UNIT = "element-steps/s"
@@ -172,12 +172,7 @@ def run_ours(args, world, rank, local, td):
     from e3sm_b200.partition import Partition
     p = config(args.config)
     if args.weak_ne:
-        # same step, finer sphere: HOMME's resolution rules keep it stable and the work per element-step
-        # unchanged -- dt ~ 1/ne, nu ~ (30/ne)^3.2 (rule quoted in the reference's thetanh namelists)
-        f = 30.0 / args.weak_ne
-        p = p.with_(ne=args.weak_ne, tstep=p.tstep * f, nu=p.nu * f ** 3.2, nu_p=p.nu_p * f ** 3.2,
-                    nu_s=p.nu_s * f ** 3.2, nu_div=p.nu_div * f ** 3.2,
-                    nu_top=p.nu_top * f)      # explicit sponge: nu_top * dt * ne^2 held fixed
+        p = weak_scaled(p, args.weak_ne)      # dt ~ 1/ne, nu ~ (30/ne)^3.2, nu_top ~ 1/ne
     part, nccl_id = None, None
     if world > 1:   # elements cut along HOMME's space-filling curve, one slice per GPU, DSS halos over NCCL
         part = Partition(p.ne, world)

@@ -60,6 +60,15 @@ def config(name):
     return table[name]
 
 
+def weak_scaled(p: "SimParams", ne: int) -> "SimParams":
+    """The same step on a finer sphere: HOMME's resolution rules dt ~ 1/ne, nu ~ (ne0/ne)^3.2 (quoted in
+    the reference's thetanh namelists) and nu_top ~ 1/ne (nu_top*dt*ne^2 fixed), so the work per
+    element-step is unchanged and the run stays stable."""
+    f = float(p.ne) / ne
+    return p.with_(ne=ne, tstep=p.tstep * f, nu=p.nu * f ** 3.2, nu_p=p.nu_p * f ** 3.2,
+                   nu_s=p.nu_s * f ** 3.2, nu_div=p.nu_div * f ** 3.2, nu_top=p.nu_top * f)
+
+
 def bytes_per_element_step(p: "SimParams", nlev_tom: int) -> int:
     """Algorithmic HBM bytes per element per dynamics step, SURVEY.md 8(d) / BASELINE.md section 3."""
     nlev = p.nlev

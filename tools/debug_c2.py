@@ -3,7 +3,7 @@ import ctypes, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from e3sm_b200.params import config
+from e3sm_b200.params import config, weak_scaled
 from e3sm_b200.dycore import ThetaLDycore, build_case
 from e3sm_b200 import lib
 L = lib.load()
@@ -12,6 +12,9 @@ nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 40
 variants = {
     "C2": config("C2"),
     "LIT": config("C2").with_(nu_div=2.5e15),
+    "W2 ne42": weak_scaled(config("C2"), 42),
+    "W4 ne60": weak_scaled(config("C2"), 60),
+    "W8 ne85": weak_scaled(config("C2"), 85),
     "C5 (hvs=3)": config("C5"),
     "C2 nu_top=0": config("C2").with_(nu_top=0.0, hypervis_subcycle_tom=0),
     "C2 nu_div=1e15": config("C2").with_(nu_div=1e15),
@@ -32,7 +35,7 @@ for name, p in variants.items():
         except RuntimeError as e:
             print("step", i, "ERROR", e, flush=True)
             break
-        if i % 10 == 9 or i == nsteps - 1:
+        if i % 50 == 49 or i == nsteps - 1:
             s = d.get_state()
             w = np.abs(s.w_i[:, n0])
             ie, k, pt = np.unravel_index(np.argmax(w), w.shape)
