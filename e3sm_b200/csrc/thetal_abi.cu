@@ -4,6 +4,7 @@
 //  H/src/share/cxx/prim_driver.cpp, mpi/mpi_cxx_f90_interface.cpp); see include/thetal_b200.h.
 #include "../../include/thetal_b200.h"
 #include "thetal_kernels.h"
+#include "thetal_reprosum.h"
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -71,6 +72,8 @@ struct Session {
   RefStates ref{};
   int *d_err = nullptr, *d_maxiter = nullptr;
   unsigned long long *d_maxdelta = nullptr;
+  double *d_diag_part = nullptr;            // [nelem][NDIAG] element integrals
+  unsigned long long *d_diag_acc = nullptr; // [NDIAG] max bits, [2] ps min/max bits, [NDIAG*3] limbs
   bool device_ready = false;
   long launches = 0;
   bool prof = false;
@@ -483,6 +486,7 @@ void init_functors_c(const int *allocate_buffer)
   S.ref.dp_ref = dalloc<double>((size_t)n * 16 * nlev);
   S.ref.phi_ref = dalloc<double>((size_t)n * 16 * (nlev + 1));
   S.d_err = dalloc<int>(1); S.d_maxiter = dalloc<int>(1); S.d_maxdelta = dalloc<unsigned long long>(1);
+  S.d_diag_part = dalloc<double>((size_t)S.prm.nelem * NDIAG); S.d_diag_acc = dalloc<unsigned long long>(NDIAG + 2 + NDIAG * thetal_reprosum::NLIMB);
   if (S.nu_scale_top.empty()) S.nu_scale_top.assign(nlev, 0.0);
   upload_constants(S.dvv, S.mp, S.hybi.data(), S.dp0.data(), S.nu_scale_top.data(), nlev);
   CUDA_OK(cudaDeviceSynchronize());
@@ -839,6 +843,44 @@ void thetal_b200_halo_lists(int *peer_rank, int *send_off, int *send_cnt, int *r
 }
 void thetal_b200_dss_table(int *dss_src) { memcpy(dss_src, S.hdss.data(), S.hdss.size() * sizeof(int)); }
 void thetal_b200_halo_stats(long *exchanges, long *bytes) { *exchanges = S.exchanges; *bytes = S.halo_bytes; }
+
+// Global diagnostics of time level *tl on the device: prim_energy_halftimes
+// (prim_state_mod.F90:822-939) + global_integral (global_norms_mod.F90:47-90, divided by the 4 pi
+// domain size) with an order-independent sum, so every rank of every partition gets the same bits.
+//   out[0..7] = min ps, max ps, <ps>, <KE>, <PE>, <IE>, <KE+PE+IE>, elements owned by this rank
+void thetal_b200_global_diagnostics(const int *tl, double *out)
+{
+  require(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_global_diagnostics: bad state/time level");
+  constexpr int NL = thetal_reprosum::NLIMB, NACC = NDIAG + 2 + NDIAG * NL;
+  unsigned long long *maxbits = S.d_diag_acc, *psmm = S.d_diag_acc + NDIAG, *limbs = S.d_diag_acc + NDIAG + 2;
+  CUDA_OK(cudaMemsetAsync(S.d_diag_acc, 0, NACC * sizeof(unsigned long long), S.stream));
+  CUDA_OK(cudaMemsetAsync(psmm, 0xff, sizeof(unsigned long long), S.stream));          // running min
+  DiagArgs a;
+  a.st = S.tl[*tl]; a.geo = S.geo; a.prm = S.prm; a.part = S.d_diag_part; a.maxbits = maxbits; a.ps_minmax = psmm;
+  launch_diag_elements(a, S.stream); S.launches += 1;
+  if (S.nranks > 1) {
+    NCCL_OK(ncclGroupStart());
+    NCCL_OK(ncclAllReduce(maxbits, maxbits, NDIAG, ncclUint64, ncclMax, S.comm, S.stream));
+    NCCL_OK(ncclAllReduce(psmm, psmm, 1, ncclUint64, ncclMin, S.comm, S.stream));
+    NCCL_OK(ncclAllReduce(psmm + 1, psmm + 1, 1, ncclUint64, ncclMax, S.comm, S.stream));
+    NCCL_OK(ncclGroupEnd());
+  }
+  launch_diag_accumulate(S.d_diag_part, S.prm.nelem, maxbits, limbs, S.stream); S.launches += 1;
+  if (S.nranks > 1) NCCL_OK(ncclAllReduce(limbs, limbs, NDIAG * NL, ncclInt64, ncclSum, S.comm, S.stream));
+  unsigned long long h[NACC];
+  CUDA_OK(cudaMemcpyAsync(h, S.d_diag_acc, sizeof h, cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  check_device_errors("thetal_b200_global_diagnostics");
+  memcpy(&out[0], &h[NDIAG], 8); memcpy(&out[1], &h[NDIAG + 1], 8);
+  const double four_pi = 4.0 * 3.14159265358979323846264338327950288;       // dd_pi, physical_constants.F90:48
+  for (int q = 0; q < NDIAG; q++) {
+    long long l[NL];
+    for (int j = 0; j < NL; j++) l[j] = (long long)h[NDIAG + 2 + q * NL + j];
+    out[2 + q] = thetal_reprosum::combine(l, thetal_reprosum::exponent_of_bits(h[q])) / four_pi;
+  }
+  out[6] = out[3] + out[4] + out[5];
+  out[7] = (double)S.prm.nelem;      // elements owned by this rank
+}
 
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);

@@ -12,6 +12,7 @@
 // gather from the neighbours' pre-DSS ("tens") values, so there are no edge buffers.
 #include "thetal_kernels.h"
 #include "thetal_pow.h"
+#include "thetal_reprosum.h"
 #include <cstdio>
 
 namespace thetal {
@@ -1428,6 +1429,83 @@ void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, in
 {
   const long n = (long)nent * (6 * nk + wbot);
   if (n > 0) halo_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, idx, nent, nk, wbot, nlev, buf);
+}
+
+// ---------------------------------------------------------------- global diagnostics
+// prim_energy_halftimes (prim_state_mod.F90:822-939) per element, then global_integral
+// (global_norms_mod.F90:47-90): J(ie) = sum_{j,i} spheremp * h in the reference's point order, and
+// an order-independent fixed-point sum over elements (thetal_reprosum.h).
+//   q = 0: ps = ptop + sum_k dp3d        1: KE = sum_k dp (u^2+v^2)/2 + dp (w_k^2+w_k+1^2)/4
+//   q = 2: PE = sum_k dp (phi_k+phi_k+1)/2   3: IE = sum_k cp vtheta_dp exner + dphi pnh, + ptop phi_top
+__global__ void __launch_bounds__(256) diag_element_kernel(const DiagArgs A)
+{
+  __shared__ double red[NDIAG][16][16];
+  __shared__ double col[NDIAG][16];
+  const int nlev = A.prm.nlev, ie = blockIdx.x, tid = threadIdx.x, p = tid & 15, ks = tid >> 4;
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * (nlev + 1), ev = (size_t)ie * 32 * nlev;
+  double s_ps = 0, s_ke = 0, s_pe = 0, s_ie = 0;
+  for (int k = ks; k < nlev; k += 16) {
+    const int q = k * 16 + p;
+    const double dp = A.st.dp[em + q], th = A.st.th[em + q];
+    const double phi0 = A.st.phi[ei + q], phi1 = A.st.phi[ei + q + 16];
+    const double w0 = A.st.w[ei + q], w1 = A.st.w[ei + q + 16];
+    const double v1 = A.st.v[ev + k * 32 + p], v2 = A.st.v[ev + k * 32 + 16 + p];
+    const double dphi = phi1 - phi0;
+    const double poe = div_fast(RGAS * th, -dphi);
+    const double pnh = eos_pnh(poe), exner = div_fast(pnh, poe);
+    s_ps += dp;
+    s_ke += 0.5 * (v1 * v1 + v2 * v2) * dp + 0.25 * (w0 * w0 + w1 * w1) * dp;
+    s_pe += 0.5 * (phi0 + phi1) * dp;
+    s_ie += CP * th * exner + dphi * pnh;
+  }
+  red[0][ks][p] = s_ps; red[1][ks][p] = s_ke; red[2][ks][p] = s_pe; red[3][ks][p] = s_ie;
+  __syncthreads();
+  if (tid < NDIAG * 16) {
+    const int q = tid >> 4;
+    double s = 0;
+    for (int j = 0; j < 16; j++) s += red[q][j][p];
+    if (q == 0) s += A.prm.ptop;
+    if (q == 3) s += A.prm.ptop * A.st.phi[ei + p];
+    col[q][p] = s;
+  }
+  __syncthreads();
+  if (tid < NDIAG) {
+    double J = 0;
+    for (int j = 0; j < 16; j++) J += A.geo.spheremp[(size_t)ie * 16 + j] * col[tid][j];
+    A.part[(size_t)ie * NDIAG + tid] = J;
+    atomicMax(A.maxbits + tid, (unsigned long long)__double_as_longlong(fabs(J)));
+  } else if (tid == 32) {
+    double lo = col[0][0], hi = col[0][0];
+    for (int j = 1; j < 16; j++) { lo = fmin(lo, col[0][j]); hi = fmax(hi, col[0][j]); }
+    atomicMin(A.ps_minmax, (unsigned long long)__double_as_longlong(lo));      // ps > 0: bit order = value order
+    atomicMax(A.ps_minmax + 1, (unsigned long long)__double_as_longlong(hi));
+  }
+}
+
+__global__ void __launch_bounds__(256) diag_accumulate_kernel(const double *part, int nelem,
+                                                              const unsigned long long *maxbits,
+                                                              unsigned long long *limbs)
+{
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  for (int q = 0; q < NDIAG; q++) {
+    long long l[thetal_reprosum::NLIMB] = {0, 0, 0};
+    if (i < nelem) thetal_reprosum::split(part[(size_t)i * NDIAG + q], thetal_reprosum::exponent_of_bits(maxbits[q]), l);
+    for (int j = 0; j < thetal_reprosum::NLIMB; j++) {
+      long long x = l[j];
+      for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
+      if ((threadIdx.x & 31) == 0 && x != 0) atomicAdd(limbs + q * thetal_reprosum::NLIMB + j, (unsigned long long)x);
+    }
+  }
+}
+
+void launch_diag_elements(const DiagArgs &A, cudaStream_t st)
+{
+  diag_element_kernel<<<A.prm.nelem, 256, 0, st>>>(A);
+}
+void launch_diag_accumulate(const double *part, int nelem, const unsigned long long *maxbits,
+                            unsigned long long *limbs, cudaStream_t st)
+{
+  diag_accumulate_kernel<<<(nelem + 255) / 256, 256, 0, st>>>(part, nelem, maxbits, limbs);
 }
 
 }  // namespace thetal

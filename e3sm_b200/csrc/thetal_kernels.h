@@ -54,6 +54,16 @@ struct ComboArgs {
   int kind;              // 9 or 5
 };
 
+constexpr int NDIAG = 4;    // ps, KE, PE, IE
+struct DiagArgs {
+  StatePtrs st;
+  Geo geo;
+  Params prm;
+  double *part;                    // [nelem][NDIAG] element integrals J(ie)
+  unsigned long long *maxbits;     // [NDIAG] running max |J| as bits
+  unsigned long long *ps_minmax;   // [2] min / max surface pressure as bits
+};
+
 void upload_constants(const double *dvv, const double *mp, const double *hybi, const double *dp0,
                       const double *nu_scale_top, int nlev);
 void launch_caar_pre(const CaarArgs &A, cudaStream_t st);
@@ -65,6 +75,9 @@ void launch_halo_pack(const StatePtrs &t, const int *idx, int nent, int nk, int 
                       cudaStream_t st);
 void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev,
                         const double *buf, cudaStream_t st);
+void launch_diag_elements(const DiagArgs &A, cudaStream_t st);
+void launch_diag_accumulate(const double *part, int nelem, const unsigned long long *maxbits,
+                            unsigned long long *limbs, cudaStream_t st);
 void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st);
 
 }  // namespace thetal

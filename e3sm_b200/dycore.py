@@ -231,6 +231,16 @@ class ThetaLDycore:
         return {"nghost": ng.value, "peers": peers, "send_idx": sidx[:ns.value], "recv_idx": ridx[:nr.value],
                 "dss_src": dss}
 
+    def global_diagnostics(self, tl):
+        """prim_energy_halftimes + global_integral of time level tl on the device (prim_state_mod.F90:822-939,
+        global_norms_mod.F90:47-90): dict ps_min, ps_max, ps_mean, KE, PE, IE, energy (integral / 4 pi).
+        Order-independent sum: the same bits on every rank of every partition."""
+        out = np.zeros(8)
+        self.L.thetal_b200_global_diagnostics(_ci(tl), c_void_p(out.ctypes.data))
+        self._check()
+        keys = ("ps_min", "ps_max", "ps_mean", "KE", "PE", "IE", "energy")
+        return {k: float(out[i]) for i, k in enumerate(keys)}
+
     def halo_stats(self):
         ex, by = ctypes.c_long(0), ctypes.c_long(0)
         self.L.thetal_b200_halo_stats(byref(ex), byref(by))

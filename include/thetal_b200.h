@@ -136,6 +136,14 @@ void thetal_b200_halo_lists(int *peer_rank, int *send_off, int *send_cnt, int *r
                             int *send_idx, int *recv_idx);
 void thetal_b200_dss_table(int *dss_src);
 void thetal_b200_halo_stats(long *exchanges, long *bytes);
+
+/* Global diagnostics of one time level, computed on the device.  Replaces the Fortran
+ * side's prim_energy_halftimes + global_integral + wrap_repro_sum for the quantities prim_printstate
+ * reports (H/src/theta-l/share/prim_state_mod.F90:822-939, :387-429; H/src/share/global_norms_mod.F90:47-90).
+ * tl is 0-based.  out[8] = min ps, max ps, <ps>, <KE>, <PE>, <IE>, <KE+PE+IE> (global_integral's
+ * convention: integral / 4 pi), elements owned by this rank.  The sum over elements is an
+ * order-independent fixed-point sum: identical bits on every rank and for every partition. */
+void thetal_b200_global_diagnostics(const int *tl, double *out);
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);
 

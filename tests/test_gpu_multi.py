@@ -55,7 +55,8 @@ def _rank_main(rank, world, port, cfg, over, nsteps, q):
         tl = _run_steps(d, p, nsteps)
         out = d.get_state()
         ex, by = d.halo_stats()
-        q.put((rank, {f: getattr(out, f)[:, tl].copy() for f in FIELDS}, ex, by))
+        diag = d.global_diagnostics(tl)
+        q.put((rank, {f: getattr(out, f)[:, tl].copy() for f in FIELDS}, ex, by, diag))
         td.barrier()
         d.close()
     finally:
@@ -95,6 +96,7 @@ def test_partitioned_run_equals_single_gpu_bitwise(world, over):
     d.set_state(st)
     tl = _run_steps(d, p, nsteps)
     one = d.get_state()
+    diag_one = d.global_diagnostics(tl)
     d.close()
     for f in FIELDS:
         multi = np.concatenate([r[1][f] for r in res], axis=0)
@@ -103,3 +105,5 @@ def test_partitioned_run_equals_single_gpu_bitwise(world, over):
         assert np.array_equal(multi, single), f"{f}: partitioned run differs from the single-GPU run"
     for r in res:
         assert r[2] > 0 and r[3] > 0          # every rank really exchanged halos
+        # device diagnostics: order-independent sum + NCCL all-reduce of integers = the single-GPU bits
+        assert r[4] == diag_one, f"rank {r[0]}: {r[4]} != {diag_one}"

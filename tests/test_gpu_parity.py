@@ -181,9 +181,35 @@ def test_ten_day_baroclinic_wave_diagnostics(case_c1):
     for a, b, name in zip(dg, do, ("min ps", "mass", "total energy")):
         assert abs(a - b) <= 1e-6 * abs(b), (name, a, b)
     assert abs(dg[1] - d0[1]) <= 1e-12 * d0[1]          # dry mass is conserved by the step
+    dev = d.global_diagnostics(n0)                       # the same numbers computed on the device (N3)
+    four_pi = 4.0 * np.pi
+    assert abs(dev["ps_min"] - do[0]) <= 1e-6 * do[0]
+    assert abs(dev["ps_mean"] * four_pi - do[1]) <= 1e-6 * do[1]
+    assert abs(dev["energy"] * four_pi - do[2]) <= 1e-6 * abs(do[2])
     assert dg[0] < d0[0] - 100.0                         # and the wave really developed
     for f in ("v", "vtheta_dp", "phinh_i", "dp3d"):     # the fields themselves are still close
         assert rel_l2(getattr(sg, f)[:, n0], getattr(so, f)[:, n0]) <= 1e-6, f
+    d.close()
+
+
+def test_device_global_diagnostics_match_host_formulas(case_c1, parity_state_c1):
+    """thetal_b200_global_diagnostics (device, order-independent sum) against the numpy restatement of
+    prim_energy_halftimes + global_integral on the same state; repeated calls give the same bits."""
+    from conftest import global_diagnostics
+    p, grid, hv = case_c1[0], case_c1[1], case_c1[2]
+    p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
+    d.prim_advance_exp(p.tstep, 0, 1, 2)
+    sg = d.get_state()
+    for tl in (1, 2):
+        ps_min, mass, energy = global_diagnostics(sg, tl, grid, hv)
+        dev = d.global_diagnostics(tl)
+        four_pi = 4.0 * np.pi
+        assert abs(dev["ps_min"] - ps_min) <= 1e-13 * ps_min
+        assert abs(dev["ps_mean"] * four_pi - mass) <= 1e-13 * mass
+        assert abs(dev["energy"] * four_pi - energy) <= 1e-12 * abs(energy)
+        assert dev["ps_max"] >= dev["ps_mean"] >= dev["ps_min"] > 0
+        assert abs(dev["KE"] + dev["PE"] + dev["IE"] - dev["energy"]) <= 1e-15 * abs(dev["energy"])
+        assert d.global_diagnostics(tl) == dev
     d.close()
 
 
