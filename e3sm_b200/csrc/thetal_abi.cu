@@ -61,6 +61,8 @@ struct Session {
   int *d_interior = nullptr, *d_boundary = nullptr;
   cudaStream_t stream2 = nullptr;
   cudaEvent_t ev_prod = nullptr, ev_halo = nullptr;
+  int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
+  int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
   int overlap = 0;          // measured on 2 and 8 B200: the split launches cost more than the hidden exchange saves
   // device
   cudaStream_t stream = nullptr;
@@ -336,10 +338,12 @@ void init_simulation_params_c(const int *remap_alg, const int *limiter_option, c
     const int *internal_diagnostics_level, const int *do_3d_turbulence,
     const double *tom_sponge_start)
 {
-  (void)remap_alg; (void)limiter_option; (void)state_frequency; (void)nu_q; (void)use_moisture;
+  (void)limiter_option; (void)state_frequency; (void)nu_q; (void)use_moisture;
   (void)disable_diagnostics; (void)use_cpstar; (void)transport_alg; (void)test_case;
   (void)dt_remap_factor; (void)dt_tracer_factor; (void)nsplit; (void)internal_diagnostics_level;
   (void)tom_sponge_start;
+  check_in("remap_alg", *remap_alg, {1, 10, 11});                     // PPM only, like cxx_f90_interface_theta.cpp:57-73
+  S.remap_alg = *remap_alg;
   check_in("hypervis_order", *hypervis_order, {2});
   check_in("time_step_type", *time_step_type, {1, 4, 5, 7, 9, 10});
   check_in("theta_advection_form", *theta_adv_form, {0, 1, 2});
@@ -489,6 +493,7 @@ void init_functors_c(const int *allocate_buffer)
   S.d_diag_part = dalloc<double>((size_t)S.prm.nelem * NDIAG); S.d_diag_acc = dalloc<unsigned long long>(NDIAG + 2 + NDIAG * thetal_reprosum::NLIMB);
   if (S.nu_scale_top.empty()) S.nu_scale_top.assign(nlev, 0.0);
   upload_constants(S.dvv, S.mp, S.hybi.data(), S.dp0.data(), S.nu_scale_top.data(), nlev);
+  upload_hyai(S.hyai.data(), nlev);
   CUDA_OK(cudaDeviceSynchronize());
   S.device_ready = true;
 }
@@ -523,6 +528,10 @@ void check_device_errors(const char *where)
   if (err & ERR_EOS_BAD_STATE) {     // eos.F90:128-145 aborts the job
     CUDA_OK(cudaMemsetAsync(S.d_err, 0, sizeof(int), S.stream));
     fail(10, std::string("EOS bad state: d(phi), dp3d or vtheta_dp < 0 (detected in ") + where + ")");
+  }
+  if (err & ERR_REMAP_NEGATIVE_LAYER) {   // vertremap_mod.F90:87-103 aborts the job
+    CUDA_OK(cudaMemsetAsync(S.d_err, 0, sizeof(int), S.stream));
+    fail(11, std::string("negative layer thickness.  timestep or remap time too large (detected in ") + where + ")");
   }
   if (err & ERR_DIRK_NOT_CONVERGED) {  // imex_mod.F90:353-357: warning only
     fprintf(stderr, "thetal_b200: WARNING: IMEX solver failed b/c max iteration count was met\n");
@@ -926,9 +935,26 @@ void prim_advance_exp_c(const double *dt, const int *nm1, const int *n0, const i
   thetal_b200_sync();
 }
 
+// vertical_remap (vertremap_mod.F90:23-171) of time level *np1 (0-based): back from the
+// floating Lagrangian levels to the reference levels with PPM (vert_remap_u_alg = remap_alg 1/10/11).
+static void run_vertical_remap(int np1)
+{
+  RemapArgs a;
+  a.st = S.tl[np1]; a.geo = S.geo; a.prm = S.prm; a.remap_alg = S.remap_alg; a.err = S.d_err;
+  launch_vertical_remap(a, S.stream); S.launches += 1;
+}
+void vertical_remap_c(const int *np1)
+{
+  require(S.device_ready && tl_ok(*np1), "vertical_remap_c: bad state/time level");
+  run_vertical_remap(*np1);
+  thetal_b200_sync();
+}
+void thetal_b200_set_vertical_remap(const int *on) { S.do_remap = *on; }
+
 // prim_run_subcycle (prim_driver_base.F90:1024-1195, prim_driver.cpp:60-181) restricted to the
-// dynamics: qsize=0, no forcing, and NO vertical remap -- each call advances
-// `rsplit` dynamics steps of length tstep and rotates the time levels (time_mod.F90:109-138).
+// dynamics: qsize=0, no forcing -- each call advances `rsplit` dynamics steps of length tstep,
+// rotates the time levels (time_mod.F90:109-138) and remaps the result to the reference levels
+// (prim_driver_base.F90:1159: vertical_remap on np1 before the last TimeLevel_update).
 void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int *np1,
                          const int *next_output_step, const int *nsplit_iter)
 {
@@ -942,6 +968,7 @@ void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int
     const int tmp = t_np1; t_np1 = t_nm1; t_nm1 = t_n0; t_n0 = tmp;                  // leapfrog update
     (*nstep)++;
   }
+  if (S.do_remap) run_vertical_remap(t_n0);        // the level just computed (np1 before the rotation)
   thetal_b200_sync();
   *nm1 = t_nm1 + 1; *n0 = t_n0 + 1; *np1 = t_np1 + 1;
   S.nm1 = t_nm1; S.n0 = t_n0; S.np1 = t_np1; S.nstep = *nstep;

@@ -55,6 +55,6 @@ struct RefStates {
 };
 
 // error flag bits written by kernels
-enum : int { ERR_EOS_BAD_STATE = 1, ERR_DIRK_NOT_CONVERGED = 2 };
+enum : int { ERR_EOS_BAD_STATE = 1, ERR_DIRK_NOT_CONVERGED = 2, ERR_REMAP_NEGATIVE_LAYER = 4 };
 
 }  // namespace thetal

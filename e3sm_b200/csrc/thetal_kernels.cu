@@ -23,6 +23,7 @@ __constant__ double c_mp[16];
 __constant__ double c_hybi[MAXLEV + 1];
 __constant__ double c_dp0[MAXLEV];
 __constant__ double c_nu_scale_top[MAXLEV];
+__constant__ double c_hyai[MAXLEV + 1];
 
 void upload_constants(const double *dvv, const double *mp, const double *hybi, const double *dp0,
                       const double *nu_scale_top, int nlev)
@@ -33,6 +34,7 @@ void upload_constants(const double *dvv, const double *mp, const double *hybi, c
   if (dp0) cudaMemcpyToSymbol(c_dp0, dp0, nlev * sizeof(double));
   if (nu_scale_top) cudaMemcpyToSymbol(c_nu_scale_top, nu_scale_top, nlev * sizeof(double));
 }
+void upload_hyai(const double *hyai, int nlev) { cudaMemcpyToSymbol(c_hyai, hyai, (nlev + 1) * sizeof(double)); }
 
 // ------------------------------------------------------------------------------------------
 // Per-thread view of one GLL point (a,b) = (i,j) of an element: derivative rows + metric terms.
@@ -1506,6 +1508,239 @@ void launch_diag_accumulate(const double *part, int nelem, const unsigned long l
                             unsigned long long *limbs, cudaStream_t st)
 {
   diag_accumulate_kernel<<<(nelem + 255) / 256, 256, 0, st>>>(part, nelem, maxbits, limbs);
+}
+
+// ---------------------------------------------------------------- vertical remap
+// vertical_remap, vertremap_mod.F90:23-171 (rsplit > 0, qsize = 0) with remap_Q_ppm
+// (vertremap_base.F90:514-646; compute_ppm_grids :650-673, compute_ppm :680-723, integrate_parabola
+// :730-737, binary_search :744-765, linextrap :768-800).  One CTA per element, 16 columns x 16 level
+// slots; the running sums (pressures, masses, phi) are kept in the reference's k order by one thread
+// per column, everything else is parallel over levels.  All arrays sit in shared memory as [row][16].
+__global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
+{
+  extern __shared__ double rsm[];
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, R = nlev + 4;
+  const int ie = blockIdx.x, tid = threadIdx.x, p = tid & 15, ks = tid >> 4;
+  double *dpo = rsm, *pio = dpo + R * 16, *pin = pio + R * 16, *z2 = pin + R * 16, *ao = z2 + R * 16;
+  double *masso = ao + R * 16, *dma = masso + R * 16, *ai = dma + R * 16, *qm = ai + R * 16;
+  double *phr = qm + R * 16, *phs = phr + R * 16, *ps = phs + R * 16;
+  int *kid = (int *)(ps + 16);
+#define DPO(i) dpo[((i) + 1) * 16 + p]
+#define AO(i) ao[((i) + 1) * 16 + p]
+#define ROW(a, k) a[(k) * 16 + p]
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  double *gdp = A.st.dp + em, *gth = A.st.th + em, *gphi = A.st.phi + ei, *gw = A.st.w + ei, *gv = A.st.v + ev;
+  const double ptop = A.prm.ptop;
+  int bad = 0;
+  for (int k = 1 + ks; k <= nlev; k += 16) {
+    const double d = gdp[(k - 1) * 16 + p];
+    DPO(k) = d;
+    if (d < 0) bad = 1;
+  }
+  if (bad) atomicOr(A.err, ERR_REMAP_NEGATIVE_LAYER);
+  if (__syncthreads_or(bad)) return;                          // the reference aborts before remapping (:87-103)
+  // phi_from_eos pieces: hydrostatic pressure scan, parallel power terms, phi scan from the bottom
+  auto phi_ref_scan = [&](const double *dprow1 /* rows 1..nlev of a [row][16] array */) {
+    if (tid < 16) {                                           // p_i(k+1) = p_i(k) + dp(k), eos.F90:287-290
+      double pi = ptop;
+      ROW(masso, 1) = pi;
+      for (int k = 1; k <= nlev; k++) { pi = pi + dprow1[k * 16 + p]; ROW(masso, k + 1) = pi; }
+    }
+    __syncthreads();
+    for (int k = 1 + ks; k <= nlev; k += 16) {                // eos.F90:300
+      const double pm = (ROW(masso, k + 1) + ROW(masso, k)) / 2;
+      ROW(ai, k) = (RGAS * gth[(k - 1) * 16 + p] * thetal_pow::pow_pos(pm / P0, C_KM1)) / P0;
+    }
+    __syncthreads();
+    if (tid < 16) {
+      double ph = A.geo.phis[(size_t)ie * 16 + p];
+      ROW(phr, nlevp) = ph;
+      for (int k = nlev; k >= 1; k--) { ph = ph + ROW(ai, k); ROW(phr, k) = ph; }
+    }
+    __syncthreads();
+  };
+  phi_ref_scan(dpo + 16);                                     // DPO(k) lives in row k+1
+  // remove the hydrostatic phi, reference layer thickness, interface pressures of both grids
+  for (int k = 1 + ks; k <= nlevp; k += 16) ROW(phs, k) = gphi[(k - 1) * 16 + p] - ROW(phr, k);
+  if (tid < 16) {
+    double s = 0;
+    for (int k = 1; k <= nlev; k++) s = s + DPO(k);
+    ps[p] = ptop + s;                                         // vertremap_mod.F90:76-77
+  }
+  __syncthreads();
+  for (int k = 1 + ks; k <= nlev; k += 16)                    // dp on reference levels, :79-80 (kept in qm for now)
+    ROW(z2, k) = (c_hyai[k] - c_hyai[k - 1]) * A.prm.ps0 + (c_hybi[k] - c_hybi[k - 1]) * ps[p];
+  __syncthreads();
+  if (tid < 16) {
+    double a = 0, b = 0;
+    ROW(pin, 1) = 0; ROW(pio, 1) = 0;
+    for (int k = 1; k <= nlev; k++) {
+      a = a + ROW(z2, k); b = b + DPO(k);
+      ROW(pin, k + 1) = a; ROW(pio, k + 1) = b;
+    }
+    ROW(pio, nlev + 2) = b + 1.;
+    ROW(pin, nlev + 1) = b;
+    DPO(0) = DPO(1); DPO(-1) = DPO(2); DPO(nlev + 1) = DPO(nlev); DPO(nlev + 2) = DPO(nlev - 1);
+  }
+  __syncthreads();
+  // new layer thickness to its own array (z2 is about to be reused): dpn lives in `dma` rows until the
+  // field loop needs dma, so copy it to global dp3d at the end from registers instead
+  double dpn_r[8];                                            // this thread's levels (nlev <= 128)
+#pragma unroll
+  for (int j = 0; j < 8; j++) { const int k = 1 + ks + 16 * j; dpn_r[j] = k <= nlev ? ROW(z2, k) : 1.0; }
+  __syncthreads();
+  for (int k = 1 + ks; k <= nlev; k += 16) {                  // old cell holding the new interface k+1
+    const double pv = ROW(pin, k + 1);
+    int kk = k;
+    if (ROW(pio, kk) <= pv) {
+      while (ROW(pio, kk) <= pv) kk = kk + 1;
+      kk = kk - 1;
+    } else {
+      int lo = 1, hi = kk;
+      while (hi > lo + 1) {
+        kk = (lo + hi) / 2;
+        if (ROW(pio, kk) > pv) hi = kk; else lo = kk;
+      }
+      kk = lo;
+    }
+    if (kk == nlev + 1) kk = nlev;
+    kid[k * 16 + p] = kk;
+    ROW(z2, k) = (pv - (ROW(pio, kk) + ROW(pio, kk + 1)) * 0.5) / DPO(kk);
+  }
+  __syncthreads();
+  for (int f = 0; f < 5; f++) {
+    for (int k = 1 + ks; k <= nlev; k += 16) {                // ttmp(:,:,k,f), vertremap_mod.F90:112-121
+      const int q = (k - 1) * 16 + p;
+      double m;
+      if (f == 0) m = gv[(k - 1) * 32 + p] * DPO(k);
+      else if (f == 1) m = gv[(k - 1) * 32 + 16 + p] * DPO(k);
+      else if (f == 2) m = gth[q];
+      else if (f == 3) m = ROW(phs, k + 1) - ROW(phs, k);
+      else m = gw[q + 16] - gw[q];
+      ROW(qm, k) = m;
+      AO(k) = m / DPO(k);
+    }
+    __syncthreads();
+    if (tid < 16) {
+      double s = 0;
+      ROW(masso, 1) = 0.;
+      for (int k = 1; k <= nlev; k++) { s = s + ROW(qm, k); ROW(masso, k + 1) = s; }
+      if (A.remap_alg == 10 || A.remap_alg == 11) {
+        const bool limit = A.remap_alg == 10;
+        double lo = AO(1), hi = AO(1);
+        if (limit) for (int k = 2; k <= nlev; k++) { lo = fmin(lo, AO(k)); hi = fmax(hi, AO(k)); }
+        auto linextrap = [&](double dx1, double dx2, double dx3, double dx4, double y1, double y2, double &y3, double &y4) {
+          const double den = (dx1 + dx2) / 2;
+          double num = den + (dx2 + dx3) / 2;
+          double a = num / den;
+          y3 = (1 - a) * y1 + a * y2;
+          num = num + (dx3 + dx4) / 2;
+          a = num / den;
+          y4 = (1 - a) * y1 + a * y2;
+          if (limit) { y3 = fmax(lo, fmin(hi, y3)); y4 = fmax(lo, fmin(hi, y4)); }
+        };
+        double y3, y4;
+        linextrap(DPO(2), DPO(1), DPO(0), DPO(-1), AO(2), AO(1), y3, y4);
+        AO(0) = y3; AO(-1) = y4;
+        linextrap(DPO(nlev - 1), DPO(nlev), DPO(nlev + 1), DPO(nlev + 2), AO(nlev - 1), AO(nlev), y3, y4);
+        AO(nlev + 1) = y3; AO(nlev + 2) = y4;
+      } else {
+        AO(0) = AO(1); AO(-1) = AO(1); AO(nlev + 1) = AO(nlev); AO(nlev + 2) = AO(nlev);
+      }
+    }
+    __syncthreads();
+    for (int j = ks; j <= nlev + 1; j += 16) {                // compute_ppm stage 1 (grid terms :660-664)
+      const double dx1 = DPO(j) / (DPO(j - 1) + DPO(j) + DPO(j + 1));
+      const double dx2 = (2. * DPO(j - 1) + DPO(j)) / (DPO(j + 1) + DPO(j));
+      const double dx3 = (DPO(j) + 2. * DPO(j + 1)) / (DPO(j - 1) + DPO(j));
+      const double dr = AO(j + 1) - AO(j), dl = AO(j) - AO(j - 1);
+      const double da = dx1 * (dx2 * dr + dx3 * dl);
+      double m = copysign(fmin(fabs(da), fmin(2. * fabs(dl), 2. * fabs(dr))), da);
+      if (dr * dl <= 0.) m = 0.;
+      ROW(dma, j) = m;
+    }
+    __syncthreads();
+    for (int j = ks; j <= nlev; j += 16) {                    // stage 2 (grid terms :667-675)
+      const double d0 = DPO(j), d1 = DPO(j + 1), dm = DPO(j - 1), d2 = DPO(j + 2);
+      const double dx4 = d0 / (d0 + d1);
+      const double dx5 = 1. / (((dm + d0) + d1) + d2);
+      const double dx6 = (2. * d1 * d0) / (d0 + d1);
+      const double dx7 = (dm + d0) / (2. * d0 + d1);
+      const double dx8 = (d2 + d1) / (2. * d1 + d0);
+      const double dx9 = d0 * (dm + d0) / (2. * d0 + d1);
+      const double dx10 = d1 * (d1 + d2) / (d0 + 2. * d1);
+      const double dr = AO(j + 1) - AO(j);
+      ROW(ai, j) = AO(j) + dx4 * dr + dx5 * (dx6 * (dx7 - dx8) * dr - dx9 * ROW(dma, j + 1) + dx10 * ROW(dma, j));
+    }
+    __syncthreads();
+    for (int k = 1 + ks; k <= nlev; k += 16) {                // stage 3 for the cell the interface sits in + integral
+      const int kk = kid[k * 16 + p];
+      const double a = AO(kk);
+      double al = ROW(ai, kk - 1), ar = ROW(ai, kk);
+      if ((ar - a) * (a - al) <= 0.) { al = a; ar = a; }
+      if ((ar - al) * (a - (al + ar) / 2.) > (ar - al) * (ar - al) / 6.) al = 3. * a - 2. * ar;
+      if ((ar - al) * (a - (al + ar) / 2.) < -((ar - al) * (ar - al)) / 6.) ar = 3. * a - 2. * al;
+      const double c0 = 1.5 * a - (al + ar) / 4., c1 = ar - al, c2 = 3. * (-2. * a + (al + ar));
+      const double x1 = -0.5, x2 = ROW(z2, k);
+      const double par = c0 * (x2 - x1) + c1 * (x2 * x2 - x1 * x1) / 0.2e1 + c2 * (x2 * x2 * x2 - x1 * x1 * x1) / 0.3e1;
+      ROW(qm, k) = ROW(masso, kk) + par * DPO(kk);            // massn2(k)
+    }
+    if (tid < 16) ROW(qm, 0) = 0.;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int k = 1 + ks + 16 * j;
+      if (k <= nlev) {
+        const double out = ROW(qm, k) - ROW(qm, k - 1);
+        const int q = (k - 1) * 16 + p;
+        if (f == 0) gv[(k - 1) * 32 + p] = out / dpn_r[j];
+        else if (f == 1) gv[(k - 1) * 32 + 16 + p] = out / dpn_r[j];
+        else if (f == 2) gth[q] = out;
+        else if (f == 3) ROW(pin, k) = out;                   // pin/pio are free after the search
+        else ROW(pio, k) = out;
+      }
+    }
+    __syncthreads();
+  }
+  if (tid < 16) {                                             // vertremap_mod.F90:131-136
+    double ph = ROW(phs, nlevp), w = gw[nlev * 16 + p];
+    for (int k = nlev; k >= 1; k--) {
+      ph = ph - ROW(pin, k); w = w - ROW(pio, k);
+      ROW(phs, k) = ph; gw[(k - 1) * 16 + p] = w;
+    }
+  }
+  // reference-level thickness into a [row][16] array for the second phi_from_eos, and into dp3d (:167)
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const int k = 1 + ks + 16 * j;
+    if (k <= nlev) { ROW(dma, k) = dpn_r[j]; gdp[(k - 1) * 16 + p] = dpn_r[j]; }
+  }
+  __syncthreads();
+  phi_ref_scan(dma);                                          // uses the remapped vtheta_dp (:139)
+  for (int k = 1 + ks; k <= nlevp; k += 16) gphi[(k - 1) * 16 + p] = ROW(phs, k) + ROW(phr, k);
+  if (tid < 16) {                                             // w b.c. from the remapped wind, :145-146
+    const double *gp = A.geo.gradphis + (size_t)ie * 32;
+    gw[nlev * 16 + p] = (gv[(nlev - 1) * 32 + p] * gp[p] + gv[(nlev - 1) * 32 + 16 + p] * gp[16 + p]) / G_GRAV;
+  }
+#undef DPO
+#undef AO
+#undef ROW
+}
+
+size_t vertical_remap_smem_bytes(int nlev)
+{
+  const size_t R = nlev + 4;
+  return (11 * R * 16 + 16) * sizeof(double) + R * 16 * sizeof(int);
+}
+void launch_vertical_remap(const RemapArgs &A, cudaStream_t st)
+{
+  static size_t configured = 0;
+  const size_t bytes = vertical_remap_smem_bytes(A.prm.nlev);
+  if (bytes > configured) {
+    cudaFuncSetAttribute(vertical_remap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    configured = bytes;
+  }
+  vertical_remap_kernel<<<A.prm.nelem, 256, bytes, st>>>(A);
 }
 
 }  // namespace thetal

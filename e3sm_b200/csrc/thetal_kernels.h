@@ -54,6 +54,14 @@ struct ComboArgs {
   int kind;              // 9 or 5
 };
 
+struct RemapArgs {
+  StatePtrs st;             // time level np1 (in/out)
+  Geo geo;
+  Params prm;
+  int remap_alg;            // vert_remap_u_alg: 1 (mirrored PPM), 10, 11 (linear extrapolation, 10 = limited)
+  int *err;
+};
+
 constexpr int NDIAG = 4;    // ps, KE, PE, IE
 struct DiagArgs {
   StatePtrs st;
@@ -78,6 +86,8 @@ void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, in
 void launch_diag_elements(const DiagArgs &A, cudaStream_t st);
 void launch_diag_accumulate(const double *part, int nelem, const unsigned long long *maxbits,
                             unsigned long long *limbs, cudaStream_t st);
+void upload_hyai(const double *hyai, int nlev);
+void launch_vertical_remap(const RemapArgs &A, cudaStream_t st);
 void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st);
 
 }  // namespace thetal

@@ -98,7 +98,7 @@ class ThetaLDycore:
         p = params
         name = c_char_p(b"jw_baroclinic")
         L.init_simulation_params_c(
-            _ci(1), _ci(9), _ci(p.rsplit), _ci(p.qsplit), _ci(p.tstep_type), _ci(0), _ci(0),
+            _ci(p.vert_remap_u_alg), _ci(9), _ci(p.rsplit), _ci(p.qsplit), _ci(p.tstep_type), _ci(0), _ci(0),
             _cd(p.nu), _cd(p.nu_p), _cd(0.0), _cd(p.nu_s), _cd(p.nu_div), _cd(p.nu_top),
             _ci(p.hypervis_order), _ci(p.hypervis_subcycle), _ci(p.hypervis_subcycle_tom),
             _cd(p.hypervis_scaling), _cd(0.0), _cd(0.0),
@@ -203,6 +203,15 @@ class ThetaLDycore:
         self.L.prim_run_subcycle_c(_cd(dt), byref(a), byref(b), byref(c), byref(d), _ci(0), _ci(0))
         self._check()
         return a.value, b.value, c.value, d.value
+
+    def vertical_remap(self, np1):
+        """vertremap_mod.F90:23-171 on time level np1 (0-based)."""
+        self.L.vertical_remap_c(_ci(np1))
+        self._check()
+
+    def set_vertical_remap(self, on):
+        """whether prim_run_subcycle remaps after its rsplit steps (default on, as the reference)."""
+        self.L.thetal_b200_set_vertical_remap(_ci(1 if on else 0))
 
     def time_steps(self, dt, nsteps, nm1, n0, np1):
         """Run nsteps dynamics steps back to back; returns (device ms, nm1, n0, np1)."""

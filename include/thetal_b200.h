@@ -137,6 +137,15 @@ void thetal_b200_halo_lists(int *peer_rank, int *send_off, int *send_cnt, int *r
 void thetal_b200_dss_table(int *dss_src);
 void thetal_b200_halo_stats(long *exchanges, long *bytes);
 
+/* Vertical remap of time level *np1 (0-based) from the Lagrangian levels back to the reference levels
+ * (SURVEY 8f N1).  Replaces vertical_remap, H/src/theta-l/share/vertremap_mod.F90:23-171 (rsplit > 0,
+ * qsize = 0) with remap_Q_ppm, H/src/share/vertremap_base.F90:514-646; the algorithm is the remap_alg
+ * given to init_simulation_params_c (1, 10 or 11 -- the PPM family HOMMEXX supports).  A negative
+ * layer thickness is fatal (code 11) as in vertremap_mod.F90:87-103.  prim_run_subcycle_c calls it
+ * after its rsplit dynamics steps unless thetal_b200_set_vertical_remap(0) was called. */
+void vertical_remap_c(const int *np1);
+void thetal_b200_set_vertical_remap(const int *on);
+
 /* Global diagnostics of one time level, computed on the device.  Replaces the Fortran
  * side's prim_energy_halftimes + global_integral + wrap_repro_sum for the quantities prim_printstate
  * reports (H/src/theta-l/share/prim_state_mod.F90:822-939, :387-429; H/src/share/global_norms_mod.F90:47-90).

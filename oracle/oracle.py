@@ -122,6 +122,10 @@ class Oracle:
     def advance_hypervis(self, nt, dt2, eta_ave_w):
         self.lib.orc_advance_hypervis(byref(self.c), c_int(nt), c_double(dt2), c_double(eta_ave_w))
 
+    def vertical_remap(self, np1, remap_alg=1):
+        """vertremap_mod.F90:23-171 (rsplit>0, qsize=0) with remap_Q_ppm; returns 1 on a negative layer."""
+        return int(self.lib.orc_vertical_remap(byref(self.c), c_int(np1), c_int(remap_alg)))
+
     def prim_advance_exp(self, dt, nm1, n0, np1):
         self.lib.orc_prim_advance_exp(byref(self.c), c_int(self.params.tstep_type), c_double(dt), c_int(nm1),
                                       c_int(n0), c_int(np1), c_int(self.params.qsplit))

@@ -1149,3 +1149,199 @@ void orc_prim_advance_exp(orc_ctx *c, int tstep_type, double dt, int nm1, int n0
   }
   if (c->nu > 0) orc_advance_hypervis(c, np1, dt, eta_ave_w);                              /* PA:499-500 */
 }
+
+/* ---------------- vertical remap ---------------- */
+/* linextrap, H/src/share/vertremap_base.F90:768-800 */
+static void linextrap(double dx1, double dx2, double dx3, double dx4, double y1, double y2,
+                      double *y3, double *y4, int limit, double lo, double hi)
+{
+  double den = (dx1 + dx2) / 2;
+  double num = den + (dx2 + dx3) / 2;
+  double a = num / den;
+  *y3 = (1 - a) * y1 + a * y2;
+  num = num + (dx3 + dx4) / 2;
+  a = num / den;
+  *y4 = (1 - a) * y1 + a * y2;
+  if (limit) {
+    *y3 = fmax(lo, fmin(hi, *y3));
+    *y4 = fmax(lo, fmin(hi, *y4));
+  }
+}
+
+/* remap_Q_ppm for one column, H/src/share/vertremap_base.F90:514-646 with compute_ppm_grids :650-673,
+ * compute_ppm :680-723, integrate_parabola :730-737, binary_search :744-765.
+ * q[f][k] at stride (fstride, kstride); dp1/dp2 at stride kstride.  remap_alg 1, 10 or 11. */
+static void remap_q_ppm_column(int nlev, int nf, double *q, size_t fstride, size_t kstride,
+                               const double *dp1, const double *dp2, int remap_alg, double *work)
+{
+  /* arrays with Fortran bounds mapped to offsets: X(1-gs:nlev+gs) -> X[i+1] for index i>=-1 */
+  double *pio = work;                     /* pio(1:nlev+2)  -> pio[k]  (k 1-based, slot 0 unused) */
+  double *pin = pio + (nlev + 3);         /* pin(1:nlev+1) */
+  double *masso = pin + (nlev + 2);       /* masso(1:nlev+1) */
+  double *ao = masso + (nlev + 2);        /* ao(-1:nlev+2) -> ao[i+1] */
+  double *dpo = ao + (nlev + 4);          /* dpo(-1:nlev+2) -> dpo[i+1] */
+  double *z2 = dpo + (nlev + 4);          /* z2(1:nlev) */
+  double *dma = z2 + (nlev + 1);          /* dma(0:nlev+1) */
+  double *ai = dma + (nlev + 2);          /* ai(0:nlev) */
+  double *coefs = ai + (nlev + 1);        /* coefs(0:2,1:nlev) -> coefs[3*j+m] */
+  double *ppmdx = coefs + 3 * (nlev + 1); /* ppmdx(1:10,0:nlev+1) -> ppmdx[10*j + (m-1)] */
+  int *kid = (int *)(ppmdx + 10 * (nlev + 2));
+#define AO(i) ao[(i) + 1]
+#define DPO(i) dpo[(i) + 1]
+#define DX(m, j) ppmdx[10 * (j) + (m) - 1]
+  pin[1] = 0; pio[1] = 0;
+  for (int k = 1; k <= nlev; k++) {
+    DPO(k) = dp1[(k - 1) * kstride];
+    pin[k + 1] = pin[k] + dp2[(k - 1) * kstride];
+    pio[k + 1] = pio[k] + DPO(k);
+  }
+  pio[nlev + 2] = pio[nlev + 1] + 1.;
+  pin[nlev + 1] = pio[nlev + 1];
+  for (int k = 1; k <= 2; k++) { DPO(1 - k) = DPO(k); DPO(nlev + k) = DPO(nlev + 1 - k); }
+  for (int k = 1; k <= nlev; k++) {
+    int kk = k;
+    if (pio[kk] <= pin[k + 1]) {
+      while (pio[kk] <= pin[k + 1]) kk = kk + 1;
+      kk = kk - 1;
+    } else {                                   /* binary_search */
+      int lo, hi;
+      if (pio[kk] > pin[k + 1]) { lo = 1; hi = kk; } else { lo = kk; hi = nlev + 2; }
+      while (hi > lo + 1) {
+        kk = (lo + hi) / 2;
+        if (pio[kk] > pin[k + 1]) hi = kk; else lo = kk;
+      }
+      kk = lo;
+    }
+    if (kk == nlev + 1) kk = nlev;
+    kid[k] = kk;
+    z2[k] = (pin[k + 1] - (pio[kk] + pio[kk + 1]) * 0.5) / DPO(kk);
+  }
+  for (int j = 0; j <= nlev + 1; j++) {        /* compute_ppm_grids */
+    DX(1, j) = DPO(j) / (DPO(j - 1) + DPO(j) + DPO(j + 1));
+    DX(2, j) = (2. * DPO(j - 1) + DPO(j)) / (DPO(j + 1) + DPO(j));
+    DX(3, j) = (DPO(j) + 2. * DPO(j + 1)) / (DPO(j - 1) + DPO(j));
+  }
+  for (int j = 0; j <= nlev; j++) {
+    DX(4, j) = DPO(j) / (DPO(j) + DPO(j + 1));
+    DX(5, j) = 1. / (((DPO(j - 1) + DPO(j)) + DPO(j + 1)) + DPO(j + 2));
+    DX(6, j) = (2. * DPO(j + 1) * DPO(j)) / (DPO(j) + DPO(j + 1));
+    DX(7, j) = (DPO(j - 1) + DPO(j)) / (2. * DPO(j) + DPO(j + 1));
+    DX(8, j) = (DPO(j + 2) + DPO(j + 1)) / (2. * DPO(j + 1) + DPO(j));
+    DX(9, j) = DPO(j) * (DPO(j - 1) + DPO(j)) / (2. * DPO(j) + DPO(j + 1));
+    DX(10, j) = DPO(j + 1) * (DPO(j + 1) + DPO(j + 2)) / (DPO(j) + 2. * DPO(j + 1));
+  }
+  for (int f = 0; f < nf; f++) {
+    double *Q = q + f * fstride;
+    masso[1] = 0.;
+    for (int k = 1; k <= nlev; k++) {
+      AO(k) = Q[(k - 1) * kstride];
+      masso[k + 1] = masso[k] + AO(k);
+      AO(k) = AO(k) / DPO(k);
+    }
+    if (remap_alg == 10 || remap_alg == 11) {
+      const int limit = (remap_alg == 10);
+      double lo = 0, hi = 0;
+      if (limit) {
+        lo = hi = AO(1);
+        for (int k = 2; k <= nlev; k++) { lo = fmin(lo, AO(k)); hi = fmax(hi, AO(k)); }
+      }
+      linextrap(DPO(2), DPO(1), DPO(0), DPO(-1), AO(2), AO(1), &AO(0), &AO(-1), limit, lo, hi);
+      linextrap(DPO(nlev - 1), DPO(nlev), DPO(nlev + 1), DPO(nlev + 2), AO(nlev - 1), AO(nlev),
+                &AO(nlev + 1), &AO(nlev + 2), limit, lo, hi);
+    } else {
+      for (int k = 1; k <= 2; k++) { AO(1 - k) = AO(1); AO(nlev + k) = AO(nlev); }
+    }
+    for (int j = 0; j <= nlev + 1; j++) {      /* compute_ppm stage 1 */
+      double da = DX(1, j) * (DX(2, j) * (AO(j + 1) - AO(j)) + DX(3, j) * (AO(j) - AO(j - 1)));
+      double m = fmin(fabs(da), fmin(2. * fabs(AO(j) - AO(j - 1)), 2. * fabs(AO(j + 1) - AO(j))));
+      dma[j] = copysign(m, da);
+      if ((AO(j + 1) - AO(j)) * (AO(j) - AO(j - 1)) <= 0.) dma[j] = 0.;
+    }
+    for (int j = 0; j <= nlev; j++)            /* stage 2 */
+      ai[j] = AO(j) + DX(4, j) * (AO(j + 1) - AO(j)) + DX(5, j) * (DX(6, j) * (DX(7, j) - DX(8, j))
+              * (AO(j + 1) - AO(j)) - DX(9, j) * dma[j + 1] + DX(10, j) * dma[j]);
+    for (int j = 1; j <= nlev; j++) {          /* stage 3 */
+      double al = ai[j - 1], ar = ai[j];
+      if ((ar - AO(j)) * (AO(j) - al) <= 0.) { al = AO(j); ar = AO(j); }
+      if ((ar - al) * (AO(j) - (al + ar) / 2.) > (ar - al) * (ar - al) / 6.) al = 3. * AO(j) - 2. * ar;
+      if ((ar - al) * (AO(j) - (al + ar) / 2.) < -((ar - al) * (ar - al)) / 6.) ar = 3. * AO(j) - 2. * al;
+      coefs[3 * j + 0] = 1.5 * AO(j) - (al + ar) / 4.;
+      coefs[3 * j + 1] = ar - al;
+      coefs[3 * j + 2] = 3. * (-2. * AO(j) + (al + ar));
+    }
+    double massn1 = 0.;
+    for (int k = 1; k <= nlev; k++) {
+      const int kk = kid[k];
+      const double x1 = -0.5, x2 = z2[k];
+      const double *a = coefs + 3 * kk;
+      const double par = a[0] * (x2 - x1) + a[1] * (x2 * x2 - x1 * x1) / 0.2e1 + a[2] * (x2 * x2 * x2 - x1 * x1 * x1) / 0.3e1;
+      const double massn2 = masso[kk] + par * DPO(kk);
+      Q[(k - 1) * kstride] = massn2 - massn1;
+      massn1 = massn2;
+    }
+  }
+#undef AO
+#undef DPO
+#undef DX
+}
+
+/* vertical_remap, H/src/theta-l/share/vertremap_mod.F90:23-171, rsplit>0 branch, qsize = 0.
+ * Returns 1 (and sets error_flag) on a negative layer thickness (:87-103). */
+int orc_vertical_remap(orc_ctx *c, int np1, int remap_alg)
+{
+  const int nlev = c->nlev, nlevp = nlev + 1;
+  int bad = 0;
+#pragma omp parallel for num_threads(c->nthreads) schedule(static) reduction(|:bad)
+  for (int ie = 0; ie < c->nelem; ie++) {
+    double *v = c->v + off_v(c, ie, np1), *w = c->w_i + off_i(c, ie, np1);
+    double *th = c->vtheta_dp + off_m(c, ie, np1), *phi = c->phinh_i + off_i(c, ie, np1);
+    double *dp3d = c->dp3d + off_m(c, ie, np1);
+    double *dp = (double *)malloc(sizeof(double) * 16 * (7 * nlev + nlevp));
+    double *ttmp = dp + 16 * nlev, *phi_ref = ttmp + 5 * 16 * nlev;      /* ttmp[f][k][p] */
+    double *work = (double *)malloc(sizeof(double) * (24 * (nlev + 4) + 64));
+    double ps[NPSQ];
+    for (int p = 0; p < NPSQ; p++) {
+      double s = 0;                                                      /* sum(dp3d,3) */
+      for (int k = 0; k < nlev; k++) s = s + dp3d[k * 16 + p];
+      ps[p] = c->hyai[0] * c->ps0 + s;
+    }
+    for (int k = 0; k < nlev; k++)
+      for (int p = 0; p < NPSQ; p++) {
+        dp[k * 16 + p] = (c->hyai[k + 1] - c->hyai[k]) * c->ps0 + (c->hybi[k + 1] - c->hybi[k]) * ps[p];
+        if (dp3d[k * 16 + p] < 0) bad |= 1;
+      }
+    orc_phi_from_eos(c, c->phis + (size_t)ie * 16, th, dp3d, phi_ref);
+    for (int i = 0; i < 16 * nlevp; i++) phi[i] = phi[i] - phi_ref[i];
+    for (int k = 0; k < nlev; k++)
+      for (int p = 0; p < NPSQ; p++) {
+        const double ds = dp3d[k * 16 + p];
+        ttmp[(0 * nlev + k) * 16 + p] = v[k * 32 + p] * ds;
+        ttmp[(1 * nlev + k) * 16 + p] = v[k * 32 + 16 + p] * ds;
+        ttmp[(2 * nlev + k) * 16 + p] = th[k * 16 + p];
+        ttmp[(3 * nlev + k) * 16 + p] = phi[(k + 1) * 16 + p] - phi[k * 16 + p];
+        ttmp[(4 * nlev + k) * 16 + p] = w[(k + 1) * 16 + p] - w[k * 16 + p];
+      }
+    for (int p = 0; p < NPSQ; p++)
+      remap_q_ppm_column(nlev, 5, ttmp + p, (size_t)16 * nlev, 16, dp3d + p, dp + p, remap_alg, work);
+    for (int k = 0; k < nlev; k++)
+      for (int p = 0; p < NPSQ; p++) {
+        v[k * 32 + p] = ttmp[(0 * nlev + k) * 16 + p] / dp[k * 16 + p];
+        v[k * 32 + 16 + p] = ttmp[(1 * nlev + k) * 16 + p] / dp[k * 16 + p];
+        th[k * 16 + p] = ttmp[(2 * nlev + k) * 16 + p];
+      }
+    for (int k = nlev - 1; k >= 0; k--)
+      for (int p = 0; p < NPSQ; p++) {
+        phi[k * 16 + p] = phi[(k + 1) * 16 + p] - ttmp[(3 * nlev + k) * 16 + p];
+        w[k * 16 + p] = w[(k + 1) * 16 + p] - ttmp[(4 * nlev + k) * 16 + p];
+      }
+    orc_phi_from_eos(c, c->phis + (size_t)ie * 16, th, dp, phi_ref);
+    for (int i = 0; i < 16 * nlevp; i++) phi[i] = phi[i] + phi_ref[i];
+    const double *gp = c->gradphis + (size_t)ie * 32;
+    for (int p = 0; p < NPSQ; p++)
+      w[nlev * 16 + p] = (v[(nlev - 1) * 32 + p] * gp[p] + v[(nlev - 1) * 32 + 16 + p] * gp[16 + p]) / g_;
+    for (int i = 0; i < 16 * nlev; i++) dp3d[i] = dp[i];
+    free(work); free(dp);
+  }
+  if (bad) c->error_flag |= 4;
+  return bad;
+}

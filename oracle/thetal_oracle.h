@@ -67,6 +67,7 @@ void orc_caar_pre(orc_ctx *c, int np1, int nm1, int n0, double dt2, double eta_a
 void orc_dirk(orc_ctx *c, int nm1, double alphadt_nm1, int n0, double alphadt_n0, int np1,
               double dt2, int *itercount, double *itererr);
 void orc_advance_hypervis(orc_ctx *c, int nt, double dt2, double eta_ave_w);
+int orc_vertical_remap(orc_ctx *c, int np1, int remap_alg);   /* vertremap_mod.F90:23-171, PPM remap_alg 1/10/11 */
 void orc_prim_advance_exp(orc_ctx *c, int tstep_type, double dt, int nm1, int n0, int np1,
               int qsplit);
 void orc_limiter_dp3d_k(const orc_ctx *c, double *dp3d, double *vtheta_dp, const double *spheremp);

@@ -154,25 +154,44 @@ def test_steps_at_full_vertical_resolution(cfg, over):
     # w starts from rest: measure it against its own max with an absolute floor
     dw = float(np.abs(sg.w_i[:, n0] - so.w_i[:, n0]).max())
     assert dw <= 1e-9 * max(1.0, float(np.abs(so.w_i[:, n0]).max())), dw
+    # ... and the vertical remap that follows the rsplit = 3 steps (72 / 128 level columns)
+    assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0
+    d.vertical_remap(n0)
+    sg = d.get_state()
+    for f in ("v", "vtheta_dp", "phinh_i", "dp3d"):
+        r = rel_l2(getattr(sg, f)[:, n0], getattr(so, f)[:, n0])
+        assert r <= TOL, ("remap", cfg, over, f, r)
+    dw = float(np.abs(sg.w_i[:, n0] - so.w_i[:, n0]).max())
+    assert dw <= 1e-9 * max(1.0, float(np.abs(so.w_i[:, n0]).max())), dw
     d.close()
 
 
-def test_ten_day_baroclinic_wave_diagnostics(case_c1):
+@pytest.mark.parametrize("remap", [False, True])
+def test_ten_day_baroclinic_wave_diagnostics(case_c1, remap):
     """North-star check: 10 simulated days of the JW baroclinic wave (C1: ne4 L26, dt=600 s, 1440
     dynamics steps, tstep_type 9 + hyperviscosity + sponge); min surface pressure, dry mass and total
-    energy of the GPU run within 1e-6 relative of the oracle run.  Both runs are vertically
-    Lagrangian WITHOUT vertical remap (vertical_remap is next-row N1), which the coarse
-    ne4 wave tolerates for 10 days."""
+    energy of the GPU run within 1e-6 relative of the oracle run.  remap=True is the reference's flow:
+    prim_run_subcycle_c = rsplit Lagrangian steps + vertical_remap, 480 times; remap=False leaves the
+    levels floating for the whole run (which the coarse ne4 wave tolerates)."""
     from conftest import global_diagnostics
     p, grid, hv, st0, phis, gradphis, refs = case_c1
     p, o, so, d = make_pair(case_c1, st0.copy())
     nsteps = 1440
     nm1, n0, np1 = 0, 1, 2
-    for _ in range(nsteps):
+    for i in range(nsteps):
         o.prim_advance_exp(p.tstep, nm1, n0, np1)
         nm1, n0, np1 = n0, np1, nm1
+        if remap and i % p.rsplit == p.rsplit - 1:
+            assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0
     assert o.error_flag == 0
-    ms, g_nm1, g_n0, g_np1 = d.time_steps(p.tstep, nsteps, 0, 1, 2)
+    if remap:
+        nstep, f = 0, (1, 2, 3)
+        for _ in range(nsteps // p.rsplit):
+            nstep, *f = d.prim_run_subcycle(p.tstep, nstep, *f)
+        assert nstep == nsteps
+        g_n0 = f[1] - 1
+    else:
+        ms, g_nm1, g_n0, g_np1 = d.time_steps(p.tstep, nsteps, 0, 1, 2)
     assert g_n0 == n0
     sg = d.get_state()
     dg, do = global_diagnostics(sg, n0, grid, hv), global_diagnostics(so, n0, grid, hv)
@@ -180,7 +199,7 @@ def test_ten_day_baroclinic_wave_diagnostics(case_c1):
     print("10-day diagnostics (min ps, mass, energy): gpu", dg, "oracle", do, "initial", d0)
     for a, b, name in zip(dg, do, ("min ps", "mass", "total energy")):
         assert abs(a - b) <= 1e-6 * abs(b), (name, a, b)
-    assert abs(dg[1] - d0[1]) <= 1e-12 * d0[1]          # dry mass is conserved by the step
+    assert abs(dg[1] - d0[1]) <= 1e-11 * d0[1]          # dry mass is conserved by the step (and the remap)
     dev = d.global_diagnostics(n0)                       # the same numbers computed on the device (N3)
     four_pi = 4.0 * np.pi
     assert abs(dev["ps_min"] - do[0]) <= 1e-6 * do[0]
@@ -213,6 +232,48 @@ def test_device_global_diagnostics_match_host_formulas(case_c1, parity_state_c1)
     d.close()
 
 
+@pytest.mark.parametrize("alg", [1, 10, 11])
+def test_vertical_remap(case_c1, parity_state_c1, alg):
+    """vertical_remap (vertremap_mod.F90:23-171) after rsplit Lagrangian steps: GPU vs oracle <= 1e-10 per
+    prognostic for the three PPM variants; dp3d lands exactly on the reference levels."""
+    p0, grid, hv = case_c1[0], case_c1[1], case_c1[2]
+    case = (p0.with_(vert_remap_u_alg=alg),) + tuple(case_c1[1:])
+    p, o, so, d = make_pair(case, parity_state_c1.copy())
+    nm1, n0, np1 = 0, 1, 2
+    for _ in range(p.rsplit):
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        d.prim_advance_exp(p.tstep, nm1, n0, np1)
+        nm1, n0, np1 = n0, np1, nm1
+    before = d.get_state().dp3d[:, n0].copy()
+    assert o.vertical_remap(n0, alg) == 0
+    d.vertical_remap(n0)
+    sg = d.get_state()
+    assert_state_close(sg, so, n0, 1e-10, f"vertical_remap alg {alg}")
+    ps = hv.hyai[0] * hv.ps0 + before.sum(axis=1)
+    dpref = ((hv.hyai[1:] - hv.hyai[:-1])[None, :, None] * hv.ps0
+             + (hv.hybi[1:] - hv.hybi[:-1])[None, :, None] * ps[:, None, :])
+    assert np.abs(sg.dp3d[:, n0] - dpref).max() <= 1e-12 * dpref.max()
+    assert rel_l2(sg.dp3d[:, n0], before) > 1e-7            # the levels really had floated
+    d.close()
+
+
+def test_vertical_remap_negative_layer_is_fatal(case_c1, parity_state_c1):
+    """vertremap_mod.F90:87-103: 'negative layer thickness' aborts; here error code 11."""
+    import ctypes
+    from e3sm_b200 import lib
+    st = parity_state_c1.copy()
+    st.dp3d[3, 1, 5, 7] = -1.0
+    L = lib.load()
+    L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(0)))      # latch instead of abort()
+    try:
+        p, o, so, d = make_pair(case_c1, st)
+        with pytest.raises(RuntimeError, match="negative layer thickness"):
+            d.vertical_remap(1)
+        d.close()
+    finally:
+        L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(1)))
+
+
 def test_prim_run_subcycle(case_c1, parity_state_c1):
     """the reference entry point: rsplit dynamics steps, 1-based time levels in/out"""
     p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
@@ -220,6 +281,7 @@ def test_prim_run_subcycle(case_c1, parity_state_c1):
     for _ in range(p.rsplit):
         o.prim_advance_exp(p.tstep, nm1, n0, np1)
         nm1, n0, np1 = n0, np1, nm1
+    assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0        # prim_driver_base.F90:1159
     nstep, f_nm1, f_n0, f_np1 = d.prim_run_subcycle(p.tstep, 0, 1, 2, 3)
     assert nstep == p.rsplit and (f_nm1 - 1, f_n0 - 1, f_np1 - 1) == (nm1, n0, np1)
     assert_state_close(d.get_state(), so, n0, 1e-9, "prim_run_subcycle")

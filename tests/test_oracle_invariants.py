@@ -179,3 +179,54 @@ def test_cfl_report_matches_print_cfl_formulas():
     assert np.isclose(r["gravity_wave_dt"], 1.0 / (342.0 * x * 1.5))
     assert hypervis_is_stable(g, p) and hypervis_is_stable(g, config("C5"))
     assert not hypervis_is_stable(g, p.with_(nu=1e16, nu_div=1e16))
+
+
+@pytest.mark.parametrize("alg", [1, 10, 11])
+def test_oracle_vertical_remap_properties(alg):
+    """orc_vertical_remap (vertremap_mod.F90:23-171 + remap_Q_ppm): column masses of every remapped
+    quantity are conserved, dp3d lands on the reference levels, a second remap is the identity, and a
+    uniform wind stays uniform."""
+    from e3sm_b200.dycore import build_case
+    from e3sm_b200.params import config
+    from oracle.oracle import Oracle
+    p = config("C1").with_(vert_remap_u_alg=alg)
+    grid, hv, st, phis, gradphis, refs = build_case(p)
+    o = Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=os.cpu_count())
+    nm1, n0, np1 = 0, 1, 2
+    for _ in range(p.rsplit):
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        nm1, n0, np1 = n0, np1, nm1
+    st.v[:, n0, :, 0] = 7.0                                   # uniform mixing ratio in one component
+    b = {f: getattr(st, f)[:, n0].copy() for f in st.FIELDS}
+    assert o.vertical_remap(n0, alg) == 0
+    a = {f: getattr(st, f)[:, n0] for f in st.FIELDS}
+    col = lambda x: x.sum(axis=1)
+    assert np.allclose(col(a["dp3d"]), col(b["dp3d"]), rtol=1e-14)
+    assert np.allclose(col(a["vtheta_dp"]), col(b["vtheta_dp"]), rtol=1e-13)
+    mom_b = col(b["v"][:, :, 1] * b["dp3d"]); mom_a = col(a["v"][:, :, 1] * a["dp3d"])
+    assert np.allclose(mom_a, mom_b, rtol=1e-11, atol=1e-9 * np.abs(mom_b).max())
+    assert np.abs(a["v"][:, :, 0] - 7.0).max() <= 1e-12       # constancy
+    ps = hv.hyai[0] * hv.ps0 + col(b["dp3d"])
+    dpref = ((hv.hyai[1:] - hv.hyai[:-1])[None, :, None] * hv.ps0
+             + (hv.hybi[1:] - hv.hybi[:-1])[None, :, None] * ps[:, None, :])
+    assert np.array_equal(a["dp3d"], dpref)
+    # phi top-to-bottom span: the non-hydrostatic part is remapped as layer differences, so its column sum holds
+    assert rel_l2(a["phinh_i"], b["phinh_i"]) < 1e-3 and rel_l2(a["phinh_i"], b["phinh_i"]) > 1e-8
+    snap = {f: getattr(st, f)[:, n0].copy() for f in st.FIELDS}
+    assert o.vertical_remap(n0, alg) == 0                     # already on the reference levels
+    for f in st.FIELDS:
+        assert rel_l2(getattr(st, f)[:, n0], snap[f]) <= 1e-13, f
+    if alg == 1:                                              # monotone: no new extrema in theta
+        th_b = b["vtheta_dp"] / b["dp3d"]; th_a = a["vtheta_dp"] / a["dp3d"]
+        assert th_a.min() >= th_b.min() * (1 - 1e-12) and th_a.max() <= th_b.max() * (1 + 1e-12)
+
+
+def test_oracle_vertical_remap_negative_layer():
+    from e3sm_b200.dycore import build_case
+    from e3sm_b200.params import config
+    from oracle.oracle import Oracle
+    p = config("C1")
+    grid, hv, st, phis, gradphis, refs = build_case(p)
+    st.dp3d[2, 1, 4, 3] = -5.0
+    o = Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=2)
+    assert o.vertical_remap(1, 1) == 1 and (o.error_flag & 4)
