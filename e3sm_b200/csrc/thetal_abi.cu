@@ -61,6 +61,11 @@ struct Session {
   int *d_interior = nullptr, *d_boundary = nullptr;
   cudaStream_t stream2 = nullptr;
   cudaEvent_t ev_prod = nullptr, ev_halo = nullptr;
+  // pipelined single-step service (thetal_b200_pipeline_step)
+  StatePtrs pipe_in[2]{}, pipe_out[2]{};
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaEvent_t ev_pin[4]{}, ev_pdone[4]{}, ev_pd2h[4]{};
+  long pipe_calls = 0; bool pipe_ready = false;
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
   int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
   int overlap = 0;          // measured on 2 and 8 B200: the split launches cost more than the hidden exchange saves
@@ -170,6 +175,10 @@ void finalize_hommexx_session(void)
   if (S.stream2) cudaStreamDestroy(S.stream2);
   if (S.ev_prod) cudaEventDestroy(S.ev_prod);
   if (S.ev_halo) cudaEventDestroy(S.ev_halo);
+  if (S.pipe_ready) {
+    cudaStreamDestroy(S.s_h2d); cudaStreamDestroy(S.s_d2h);
+    for (int i = 0; i < 4; i++) { cudaEventDestroy(S.ev_pin[i]); cudaEventDestroy(S.ev_pdone[i]); cudaEventDestroy(S.ev_pd2h[i]); }
+  }
   const int dev = S.device, rank = S.rank, nranks = S.nranks, aoe = S.abort_on_error;
   const bool have_id = S.have_id;
   const ncclUniqueId id = S.nccl_id;
@@ -1040,6 +1049,82 @@ extern "C" void thetal_b200_pin_host(void *ptr, const long *bytes, const int *pi
   if (*pin) CUDA_OK(cudaHostRegister(ptr, (size_t)*bytes, cudaHostRegisterDefault));
   else CUDA_OK(cudaHostUnregister(ptr));
 }
+// ---- pipelined single-step service --------------------------------------------------------------
+// One dynamics step per call on an INDEPENDENT input: the n0 state comes from pinned host arrays
+// ([ie][k][(c)][16] of one time level), the np1 state goes to pinned host arrays.  The host->device
+// copy of call j+1, the kernels of call j and the device->host copy of call j-1 run on three streams;
+// the staging buffers change places with the time-level slots by pointer (no device copies).  The
+// device state is scratch while the pipeline is in use (slots 0,1,2 = nm1,n0,np1); outputs are
+// complete after thetal_b200_pipeline_flush().
+namespace {
+void pipeline_setup()
+{
+  const int n = S.prm.nelem, nlev = S.nlev;
+  for (int b = 0; b < 2; b++) {
+    S.pipe_in[b] = alloc_state(n, nlev); S.pipe_out[b] = alloc_state(n, nlev);
+    // the step never writes phinh_i at the surface: every buffer that can become slot np1 carries phis there,
+    // as every time level of the reference does (element_state.F90: phinh_i(:,:,nlevp,:) = phis)
+    for (double *phi : {S.pipe_in[b].phi, S.pipe_out[b].phi})
+      CUDA_OK(cudaMemcpy2DAsync(phi + (size_t)nlev * 16, 16 * (size_t)(nlev + 1) * sizeof(double), S.geo.phis,
+                                16 * sizeof(double), 16 * sizeof(double), n, cudaMemcpyDeviceToDevice, S.stream));
+  }
+  CUDA_OK(cudaStreamCreateWithFlags(&S.s_h2d, cudaStreamNonBlocking));
+  CUDA_OK(cudaStreamCreateWithFlags(&S.s_d2h, cudaStreamNonBlocking));
+  for (int i = 0; i < 4; i++) {
+    CUDA_OK(cudaEventCreateWithFlags(&S.ev_pin[i], cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&S.ev_pdone[i], cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&S.ev_pd2h[i], cudaEventDisableTiming));
+  }
+  S.pipe_calls = 0; S.pipe_ready = true;
+}
+void copy_level(const StatePtrs &d, const double *v, const double *w, const double *th, const double *phi,
+                const double *dp, bool to_device, cudaStream_t st)
+{
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+  const size_t bytes[5] = {n * 32 * nlev * 8, n * 16 * (nlev + 1) * 8, n * 16 * nlev * 8, n * 16 * (nlev + 1) * 8, n * 16 * nlev * 8};
+  double *dev[5] = {d.v, d.w, d.th, d.phi, d.dp};
+  const double *host[5] = {v, w, th, phi, dp};
+  for (int i = 0; i < 5; i++) {
+    if (to_device) CUDA_OK(cudaMemcpyAsync(dev[i], host[i], bytes[i], kind, st));
+    else CUDA_OK(cudaMemcpyAsync(const_cast<double *>(host[i]), dev[i], bytes[i], kind, st));
+  }
+}
+}  // namespace
+
+extern "C" void thetal_b200_pipeline_step(const double *dt, const double *v_in, const double *w_in,
+    const double *th_in, const double *phi_in, const double *dp_in,
+    double *v_out, double *w_out, double *th_out, double *phi_out, double *dp_out)
+{
+  require(S.device_ready, "thetal_b200_pipeline_step before init");
+  if (!S.pipe_ready) pipeline_setup();
+  const long j = S.pipe_calls++;
+  const int b = (int)(j & 1), e = (int)(j & 3), e3 = (int)((j + 1) & 3);     // e3 = (j-3) mod 4
+  // 1. input: the staging buffer was the n0 slot of call j-3
+  if (j >= 3) CUDA_OK(cudaStreamWaitEvent(S.s_h2d, S.ev_pdone[e3], 0));
+  copy_level(S.pipe_in[b], v_in, w_in, th_in, phi_in, dp_in, true, S.s_h2d);
+  CUDA_OK(cudaEventRecord(S.ev_pin[e], S.s_h2d));
+  // 2. the step: staged input becomes slot n0; slot np1 is the buffer call j-3 copied out of
+  CUDA_OK(cudaStreamWaitEvent(S.stream, S.ev_pin[e], 0));
+  if (j >= 3) CUDA_OK(cudaStreamWaitEvent(S.stream, S.ev_pd2h[e3], 0));
+  std::swap(S.tl[1], S.pipe_in[b]);
+  run_prim_advance_exp(*dt, 0, 1, 2);
+  std::swap(S.tl[2], S.pipe_out[b]);
+  CUDA_OK(cudaEventRecord(S.ev_pdone[e], S.stream));
+  // 3. output
+  CUDA_OK(cudaStreamWaitEvent(S.s_d2h, S.ev_pdone[e], 0));
+  copy_level(S.pipe_out[b], v_out, w_out, th_out, phi_out, dp_out, false, S.s_d2h);
+  CUDA_OK(cudaEventRecord(S.ev_pd2h[e], S.s_d2h));
+}
+extern "C" void thetal_b200_pipeline_flush(void)
+{
+  if (!S.pipe_ready) return;
+  CUDA_OK(cudaStreamSynchronize(S.s_h2d));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.s_d2h));
+  check_device_errors("thetal_b200_pipeline_flush");
+}
+
 // enqueue one dynamics step without synchronising (bench e2e)
 extern "C" void thetal_b200_enqueue_step(const double *dt, const int *nm1, const int *n0, const int *np1)
 {

@@ -163,6 +163,16 @@ void thetal_b200_push_level(const int *tl, const double *v, const double *w_i, c
                             const double *phinh_i, const double *dp3d);
 void thetal_b200_pull_level(const int *tl, double *v, double *w_i, double *vtheta_dp,
                             double *phinh_i, double *dp3d);
+
+/* Pipelined single-step service for independent inputs (bench e2e, ensemble-style drivers): one
+ * prim_advance_exp per call, n0 state read from pinned host arrays of ONE time level
+ * ([ie][k][(c)][16]), np1 state written to pinned host arrays.  Consecutive calls overlap their
+ * host->device copy, kernels and device->host copy on three streams; the outputs are complete after
+ * thetal_b200_pipeline_flush().  The device-resident state is scratch while this is in use. */
+void thetal_b200_pipeline_step(const double *dt, const double *v_in, const double *w_in,
+    const double *vtheta_dp_in, const double *phinh_in, const double *dp3d_in,
+    double *v_out, double *w_out, double *vtheta_dp_out, double *phinh_out, double *dp3d_out);
+void thetal_b200_pipeline_flush(void);
 void thetal_b200_pin_host(void *ptr, const long *bytes, const int *pin);   /* cudaHostRegister */
 void thetal_b200_enqueue_step(const double *dt, const int *nm1, const int *n0, const int *np1);
 

@@ -274,6 +274,37 @@ def test_vertical_remap_negative_layer_is_fatal(case_c1, parity_state_c1):
         L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(1)))
 
 
+def test_pipelined_step_service(case_c1, parity_state_c1):
+    """thetal_b200_pipeline_step: 7 overlapped calls on three different inputs reproduce, bit for bit, the
+    plain prim_advance_exp of each input (staging buffers trade places with the time-level slots)."""
+    import ctypes
+    from e3sm_b200.dycore import _cd
+    from e3sm_b200.initial import State
+    FIELDS = ("v", "w_i", "vtheta_dp", "phinh_i", "dp3d")
+    p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
+    base = parity_state_c1
+    inputs, expect = [], []
+    for m in range(3):
+        st = base.copy()
+        st.v[:, 1] *= (1.0 + 0.01 * m)
+        d.set_state(st)
+        d.prim_advance_exp(p.tstep, 0, 1, 2)
+        sg = d.get_state()
+        inputs.append({f: np.ascontiguousarray(getattr(st, f)[:, 1]) for f in FIELDS})
+        expect.append({f: getattr(sg, f)[:, 2].copy() for f in FIELDS})
+    outs = [{f: np.full_like(inputs[0][f], np.nan) for f in FIELDS} for _ in range(7)]
+    cp = lambda a: ctypes.c_void_p(a.ctypes.data)
+    for j in range(7):
+        i = inputs[j % 3]
+        d.L.thetal_b200_pipeline_step(_cd(p.tstep), *[cp(i[f]) for f in FIELDS], *[cp(outs[j][f]) for f in FIELDS])
+    d.L.thetal_b200_pipeline_flush()
+    d._check()
+    for j in range(7):
+        for f in FIELDS:
+            assert np.array_equal(outs[j][f], expect[j % 3][f]), (j, f)
+    d.close()
+
+
 def test_prim_run_subcycle(case_c1, parity_state_c1):
     """the reference entry point: rsplit dynamics steps, 1-based time levels in/out"""
     p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
