@@ -1510,13 +1510,42 @@ void launch_diag_accumulate(const double *part, int nelem, const unsigned long l
   diag_accumulate_kernel<<<(nelem + 255) / 256, 256, 0, st>>>(part, nelem, maxbits, limbs);
 }
 
+// Running sums in the reference's k order for one column (pointers already offset by the point index;
+// rows are 16 doubles apart).  Eight addends are loaded before the dependent additions start, so one
+// shared-memory latency is paid per eight levels instead of per level.
+__device__ __forceinline__ double scan_up(const double *in, double *out, double s, int nlev)
+{ // out(k+1) = out(k) + in(k), k = 1..nlev
+  for (int k0 = 1; k0 <= nlev; k0 += 8) {
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = (k0 + i <= nlev) ? in[(k0 + i) * 16] : 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (k0 + i <= nlev) { s = s + x[i]; out[(k0 + i + 1) * 16] = s; }
+  }
+  return s;
+}
+template <int SIGN>
+__device__ __forceinline__ double scan_down(const double *in, double *out, double s, int nlev)
+{ // out(k) = out(k+1) +/- in(k), k = nlev..1
+  for (int k0 = nlev; k0 >= 1; k0 -= 8) {
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = (k0 - i >= 1) ? in[(k0 - i) * 16] : 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (k0 - i >= 1) { s = SIGN > 0 ? s + x[i] : s - x[i]; out[(k0 - i) * 16] = s; }
+  }
+  return s;
+}
+
 // ---------------------------------------------------------------- vertical remap
 // vertical_remap, vertremap_mod.F90:23-171 (rsplit > 0, qsize = 0) with remap_Q_ppm
 // (vertremap_base.F90:514-646; compute_ppm_grids :650-673, compute_ppm :680-723, integrate_parabola
 // :730-737, binary_search :744-765, linextrap :768-800).  One CTA per element, 16 columns x 16 level
 // slots; the running sums (pressures, masses, phi) are kept in the reference's k order by one thread
 // per column, everything else is parallel over levels.  All arrays sit in shared memory as [row][16].
-__global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
+__global__ void __launch_bounds__(256, 2) vertical_remap_kernel(const RemapArgs A)
 {
   extern __shared__ double rsm[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1, R = nlev + 4;
@@ -1542,29 +1571,28 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
   // phi_from_eos pieces: hydrostatic pressure scan, parallel power terms, phi scan from the bottom
   auto phi_ref_scan = [&](const double *dprow1 /* rows 1..nlev of a [row][16] array */) {
     if (tid < 16) {                                           // p_i(k+1) = p_i(k) + dp(k), eos.F90:287-290
-      double pi = ptop;
-      ROW(masso, 1) = pi;
-      for (int k = 1; k <= nlev; k++) { pi = pi + dprow1[k * 16 + p]; ROW(masso, k + 1) = pi; }
+      ROW(masso, 1) = ptop;
+      scan_up(dprow1 + p, masso + p, ptop, nlev);
     }
     __syncthreads();
     for (int k = 1 + ks; k <= nlev; k += 16) {                // eos.F90:300
       const double pm = (ROW(masso, k + 1) + ROW(masso, k)) / 2;
-      ROW(ai, k) = (RGAS * gth[(k - 1) * 16 + p] * thetal_pow::pow_pos(pm / P0, C_KM1)) / P0;
+      ROW(ai, k) = div_fast(RGAS * gth[(k - 1) * 16 + p] * thetal_pow::pow_pos(div_fast(pm, P0), C_KM1), P0);
     }
     __syncthreads();
     if (tid < 16) {
-      double ph = A.geo.phis[(size_t)ie * 16 + p];
+      const double ph = A.geo.phis[(size_t)ie * 16 + p];
       ROW(phr, nlevp) = ph;
-      for (int k = nlev; k >= 1; k--) { ph = ph + ROW(ai, k); ROW(phr, k) = ph; }
+      scan_down<1>(ai + p, phr + p, ph, nlev);
     }
     __syncthreads();
   };
   phi_ref_scan(dpo + 16);                                     // DPO(k) lives in row k+1
   // remove the hydrostatic phi, reference layer thickness, interface pressures of both grids
   for (int k = 1 + ks; k <= nlevp; k += 16) ROW(phs, k) = gphi[(k - 1) * 16 + p] - ROW(phr, k);
-  if (tid < 16) {
-    double s = 0;
-    for (int k = 1; k <= nlev; k++) s = s + DPO(k);
+  if (tid < 16) {                                             // old interface pressures; their last value is sum(dp3d)
+    ROW(pio, 1) = 0;
+    const double s = scan_up(dpo + 16 + p, pio + p, 0., nlev);
     ps[p] = ptop + s;                                         // vertremap_mod.F90:76-77
   }
   __syncthreads();
@@ -1572,12 +1600,9 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
     ROW(z2, k) = (c_hyai[k] - c_hyai[k - 1]) * A.prm.ps0 + (c_hybi[k] - c_hybi[k - 1]) * ps[p];
   __syncthreads();
   if (tid < 16) {
-    double a = 0, b = 0;
-    ROW(pin, 1) = 0; ROW(pio, 1) = 0;
-    for (int k = 1; k <= nlev; k++) {
-      a = a + ROW(z2, k); b = b + DPO(k);
-      ROW(pin, k + 1) = a; ROW(pio, k + 1) = b;
-    }
+    ROW(pin, 1) = 0;
+    scan_up(z2 + p, pin + p, 0., nlev);
+    const double b = ROW(pio, nlev + 1);
     ROW(pio, nlev + 2) = b + 1.;
     ROW(pin, nlev + 1) = b;
     DPO(0) = DPO(1); DPO(-1) = DPO(2); DPO(nlev + 1) = DPO(nlev); DPO(nlev + 2) = DPO(nlev - 1);
@@ -1605,7 +1630,7 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
     }
     if (kk == nlev + 1) kk = nlev;
     kid[k * 16 + p] = kk;
-    ROW(z2, k) = (pv - (ROW(pio, kk) + ROW(pio, kk + 1)) * 0.5) / DPO(kk);
+    ROW(z2, k) = div_fast(pv - (ROW(pio, kk) + ROW(pio, kk + 1)) * 0.5, DPO(kk));
   }
   __syncthreads();
   for (int f = 0; f < 5; f++) {
@@ -1618,13 +1643,12 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
       else if (f == 3) m = ROW(phs, k + 1) - ROW(phs, k);
       else m = gw[q + 16] - gw[q];
       ROW(qm, k) = m;
-      AO(k) = m / DPO(k);
+      AO(k) = div_fast(m, DPO(k));
     }
     __syncthreads();
     if (tid < 16) {
-      double s = 0;
       ROW(masso, 1) = 0.;
-      for (int k = 1; k <= nlev; k++) { s = s + ROW(qm, k); ROW(masso, k + 1) = s; }
+      scan_up(qm + p, masso + p, 0., nlev);
       if (A.remap_alg == 10 || A.remap_alg == 11) {
         const bool limit = A.remap_alg == 10;
         double lo = AO(1), hi = AO(1);
@@ -1650,9 +1674,9 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
     }
     __syncthreads();
     for (int j = ks; j <= nlev + 1; j += 16) {                // compute_ppm stage 1 (grid terms :660-664)
-      const double dx1 = DPO(j) / (DPO(j - 1) + DPO(j) + DPO(j + 1));
-      const double dx2 = (2. * DPO(j - 1) + DPO(j)) / (DPO(j + 1) + DPO(j));
-      const double dx3 = (DPO(j) + 2. * DPO(j + 1)) / (DPO(j - 1) + DPO(j));
+      const double dx1 = div_fast(DPO(j), DPO(j - 1) + DPO(j) + DPO(j + 1));
+      const double dx2 = div_fast(2. * DPO(j - 1) + DPO(j), DPO(j + 1) + DPO(j));
+      const double dx3 = div_fast(DPO(j) + 2. * DPO(j + 1), DPO(j - 1) + DPO(j));
       const double dr = AO(j + 1) - AO(j), dl = AO(j) - AO(j - 1);
       const double da = dx1 * (dx2 * dr + dx3 * dl);
       double m = copysign(fmin(fabs(da), fmin(2. * fabs(dl), 2. * fabs(dr))), da);
@@ -1662,13 +1686,13 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
     __syncthreads();
     for (int j = ks; j <= nlev; j += 16) {                    // stage 2 (grid terms :667-675)
       const double d0 = DPO(j), d1 = DPO(j + 1), dm = DPO(j - 1), d2 = DPO(j + 2);
-      const double dx4 = d0 / (d0 + d1);
-      const double dx5 = 1. / (((dm + d0) + d1) + d2);
-      const double dx6 = (2. * d1 * d0) / (d0 + d1);
-      const double dx7 = (dm + d0) / (2. * d0 + d1);
-      const double dx8 = (d2 + d1) / (2. * d1 + d0);
-      const double dx9 = d0 * (dm + d0) / (2. * d0 + d1);
-      const double dx10 = d1 * (d1 + d2) / (d0 + 2. * d1);
+      const double dx4 = div_fast(d0, d0 + d1);
+      const double dx5 = div_fast(1., ((dm + d0) + d1) + d2);
+      const double dx6 = div_fast(2. * d1 * d0, d0 + d1);
+      const double dx7 = div_fast(dm + d0, 2. * d0 + d1);
+      const double dx8 = div_fast(d2 + d1, 2. * d1 + d0);
+      const double dx9 = div_fast(d0 * (dm + d0), 2. * d0 + d1);
+      const double dx10 = div_fast(d1 * (d1 + d2), d0 + 2. * d1);
       const double dr = AO(j + 1) - AO(j);
       ROW(ai, j) = AO(j) + dx4 * dr + dx5 * (dx6 * (dx7 - dx8) * dr - dx9 * ROW(dma, j + 1) + dx10 * ROW(dma, j));
     }
@@ -1693,8 +1717,8 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
       if (k <= nlev) {
         const double out = ROW(qm, k) - ROW(qm, k - 1);
         const int q = (k - 1) * 16 + p;
-        if (f == 0) gv[(k - 1) * 32 + p] = out / dpn_r[j];
-        else if (f == 1) gv[(k - 1) * 32 + 16 + p] = out / dpn_r[j];
+        if (f == 0) gv[(k - 1) * 32 + p] = div_fast(out, dpn_r[j]);
+        else if (f == 1) gv[(k - 1) * 32 + 16 + p] = div_fast(out, dpn_r[j]);
         else if (f == 2) gth[q] = out;
         else if (f == 3) ROW(pin, k) = out;                   // pin/pio are free after the search
         else ROW(pio, k) = out;
@@ -1702,13 +1726,8 @@ __global__ void __launch_bounds__(256) vertical_remap_kernel(const RemapArgs A)
     }
     __syncthreads();
   }
-  if (tid < 16) {                                             // vertremap_mod.F90:131-136
-    double ph = ROW(phs, nlevp), w = gw[nlev * 16 + p];
-    for (int k = nlev; k >= 1; k--) {
-      ph = ph - ROW(pin, k); w = w - ROW(pio, k);
-      ROW(phs, k) = ph; gw[(k - 1) * 16 + p] = w;
-    }
-  }
+  if (tid < 16) scan_down<-1>(pin + p, phs + p, ROW(phs, nlevp), nlev);                    // vertremap_mod.F90:131-136
+  else if (tid < 32) scan_down<-1>(pio + p, gw + p - 16, gw[nlev * 16 + p], nlev);         // out(k) -> gw[(k-1)*16+p]
   // reference-level thickness into a [row][16] array for the second phi_from_eos, and into dp3d (:167)
 #pragma unroll
   for (int j = 0; j < 8; j++) {
