@@ -961,7 +961,7 @@ void vertical_remap_c(const int *np1)
 void thetal_b200_set_vertical_remap(const int *on) { S.do_remap = *on; }
 
 // prim_run_subcycle (prim_driver_base.F90:1024-1195, prim_driver.cpp:60-181) restricted to the
-// dynamics: qsize=0, no forcing -- each call advances `rsplit` dynamics steps of length tstep,
+// dynamics: qsize=0, no forcing -- each call advances rsplit*qsplit dynamics steps of length tstep,
 // rotates the time levels (time_mod.F90:109-138) and remaps the result to the reference levels
 // (prim_driver_base.F90:1159: vertical_remap on np1 before the last TimeLevel_update).
 void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int *np1,
@@ -971,7 +971,8 @@ void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int
   require(S.device_ready, "prim_run_subcycle_c before init");
   int t_nm1 = *nm1 - 1, t_n0 = *n0 - 1, t_np1 = *np1 - 1;    // Fortran passes 1-based levels
   require(tl_ok(t_nm1) && tl_ok(t_n0) && tl_ok(t_np1), "prim_run_subcycle_c: bad time level");
-  const int nsub = S.prm.rsplit > 0 ? S.prm.rsplit : 1;
+  // prim_step_type 1 (prim_driver_base.F90:1088-1159): rsplit x prim_step, each prim_step = qsplit dynamics steps
+  const int nsub = (S.prm.rsplit > 0 ? S.prm.rsplit : 1) * (S.prm.qsplit > 0 ? S.prm.qsplit : 1);
   for (int r = 0; r < nsub; r++) {
     run_prim_advance_exp(*tstep, t_nm1, t_n0, t_np1);
     const int tmp = t_np1; t_np1 = t_nm1; t_nm1 = t_n0; t_n0 = tmp;                  // leapfrog update

@@ -305,16 +305,17 @@ def test_pipelined_step_service(case_c1, parity_state_c1):
     d.close()
 
 
-def test_prim_run_subcycle(case_c1, parity_state_c1):
-    """the reference entry point: rsplit dynamics steps, 1-based time levels in/out"""
-    p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
+@pytest.mark.parametrize("qsplit", [1, 2])
+def test_prim_run_subcycle(case_c1, parity_state_c1, qsplit):
+    """the reference entry point: rsplit x qsplit dynamics steps + vertical remap, 1-based time levels in/out"""
+    p, o, so, d = make_pair(case_c1, parity_state_c1.copy(), qsplit=qsplit)
     nm1, n0, np1 = 0, 1, 2
-    for _ in range(p.rsplit):
+    for _ in range(p.rsplit * p.qsplit):
         o.prim_advance_exp(p.tstep, nm1, n0, np1)
         nm1, n0, np1 = n0, np1, nm1
     assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0        # prim_driver_base.F90:1159
     nstep, f_nm1, f_n0, f_np1 = d.prim_run_subcycle(p.tstep, 0, 1, 2, 3)
-    assert nstep == p.rsplit and (f_nm1 - 1, f_n0 - 1, f_np1 - 1) == (nm1, n0, np1)
+    assert nstep == p.rsplit * p.qsplit and (f_nm1 - 1, f_n0 - 1, f_np1 - 1) == (nm1, n0, np1)
     assert_state_close(d.get_state(), so, n0, 1e-9, "prim_run_subcycle")
     d.close()
 
