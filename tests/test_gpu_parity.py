@@ -131,7 +131,10 @@ def test_ten_steps(case_c1):
 
 
 @pytest.mark.parametrize("cfg,over", [("C2", {}), ("C5", {}), ("C4", {}), ("C3", {}), ("C2", {"tstep_type": 10}),
-                                      ("C2", {"tstep_type": 7, "theta_advect_form": 2, "pgrad_correction": 1})])
+                                      ("C2", {"tstep_type": 7, "theta_advect_form": 2, "pgrad_correction": 1}),
+                                      # the EAMxx option set short of the tensor hyperviscosity (namelist_defaults_eamxx.xml:925-997)
+                                      ("C2", {"hv_ref_profiles": 6, "theta_advect_form": 1, "pgrad_correction": 1,
+                                              "vert_remap_u_alg": 10})])
 def test_steps_at_full_vertical_resolution(cfg, over):
     """The bench/scaling configurations at their real nlev (72 / 128 levels, their dt, hyperviscosity
     and sponge settings) on the coarse ne4 sphere: three steps from the JW state, GPU vs oracle."""
