@@ -308,6 +308,30 @@ def test_pipelined_step_service(case_c1, parity_state_c1):
     d.close()
 
 
+def test_step_is_bitwise_repeatable():
+    """The same dynamics step from the same device state gives the same bits every time (ne12 L72, 864
+    elements = several waves of CTAs): no order-dependent reduction, no shared-memory race."""
+    from e3sm_b200.dycore import ThetaLDycore, build_case
+    from e3sm_b200.params import config
+    p = config("C2").with_(ne=12, tstep=600.0, nu=2e16, nu_div=2e16, nu_p=2e16, nu_s=2e16)
+    grid, hv, st, phis, gradphis, refs = build_case(p)
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+    d.set_state(st)
+    ms, nm1, n0, np1 = d.time_steps(p.tstep, 3, 0, 1, 2)
+    base = d.get_state()
+    outs = []
+    for _ in range(4):
+        d.set_state(base)
+        d.prim_advance_exp(p.tstep, nm1, n0, np1)
+        d.vertical_remap(np1)
+        s = d.get_state()
+        outs.append({f: getattr(s, f)[:, np1].copy() for f in s.FIELDS})
+    for o in outs[1:]:
+        for f in base.FIELDS:
+            assert np.isfinite(o[f]).all() and np.array_equal(o[f], outs[0][f]), f
+    d.close()
+
+
 @pytest.mark.parametrize("qsplit", [1, 2])
 def test_prim_run_subcycle(case_c1, parity_state_c1, qsplit):
     """the reference entry point: rsplit x qsplit dynamics steps + vertical remap, 1-based time levels in/out"""
