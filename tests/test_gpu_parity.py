@@ -308,6 +308,21 @@ def test_pipelined_step_service(case_c1, parity_state_c1):
     d.close()
 
 
+def test_prim_run_subcycle_against_committed_fixture(case_c1):
+    """prim_run_subcycle_c from the JW initial state against tests/golden/oracle_c1_3steps_remap.json (a
+    regression fixture written by the oracle, tools/make_golden.py): nothing on this path runs the oracle."""
+    from conftest import global_diagnostics
+    from test_oracle_invariants import _check_against_fixture
+    from e3sm_b200.dycore import ThetaLDycore
+    p, grid, hv, st0, phis, gradphis, refs = case_c1
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+    d.set_state(st0.copy())
+    nstep, f_nm1, f_n0, f_np1 = d.prim_run_subcycle(p.tstep, 0, 1, 2, 3)
+    sg = d.get_state()
+    _check_against_fixture(sg, f_n0 - 1, global_diagnostics(sg, f_n0 - 1, grid, hv), 1e-9)
+    d.close()
+
+
 def test_step_is_bitwise_repeatable():
     """The same dynamics step from the same device state gives the same bits every time (ne12 L72, 864
     elements = several waves of CTAs): no order-dependent reduction, no shared-memory race."""

@@ -230,3 +230,27 @@ def test_oracle_vertical_remap_negative_layer():
     st.dp3d[2, 1, 4, 3] = -5.0
     o = Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=2)
     assert o.vertical_remap(1, 1) == 1 and (o.error_flag & 4)
+
+
+def _check_against_fixture(st, tl, diag, tol):
+    import json
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_c1_3steps_remap.json")
+    gold = json.load(open(path))
+    assert tl == gold["time_level"]
+    for a, b in zip(diag, gold["diagnostics"]):
+        assert abs(a - b) <= tol * abs(b)
+    for f, g in gold["fields"].items():
+        x = getattr(st, f)[:, tl].ravel()
+        scale = np.sqrt(g["sumsq"] / x.size)
+        assert abs(np.sum(x * x) - g["sumsq"]) <= tol * g["sumsq"], f
+        assert np.abs(x[np.array(g["idx"])] - np.array(g["val"])).max() <= tol * scale * 10, f
+
+
+def test_oracle_matches_regression_fixture():
+    """tests/golden/oracle_c1_3steps_remap.json (tools/make_golden.py): a regression fixture of the oracle itself
+    (three C1 steps + remap) -- not a reference-generated vector; parity with the Fortran build stays unpinned."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    from make_golden import oracle_run
+    st, tl, diag = oracle_run()
+    _check_against_fixture(st, tl, diag, 1e-12)
