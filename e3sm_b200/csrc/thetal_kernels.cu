@@ -1560,6 +1560,12 @@ __global__ void __launch_bounds__(256, 2) vertical_remap_kernel(const RemapArgs 
   const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
   double *gdp = A.st.dp + em, *gth = A.st.th + em, *gphi = A.st.phi + ei, *gw = A.st.w + ei, *gv = A.st.v + ev;
   const double ptop = A.prm.ptop;
+  if (tid < 4) {      // the columns the field loop reads later, towards L2 now
+    if (tid == 0) prefetch_l2(gth, (unsigned)(16 * nlev * 8));
+    if (tid == 1) prefetch_l2(gphi, (unsigned)(16 * nlevp * 8));
+    if (tid == 2) prefetch_l2(gv, (unsigned)(32 * nlev * 8));
+    if (tid == 3) prefetch_l2(gw, (unsigned)(16 * nlevp * 8));
+  }
   int bad = 0;
   for (int k = 1 + ks; k <= nlev; k += 16) {
     const double d = gdp[(k - 1) * 16 + p];
