@@ -101,13 +101,18 @@ void fail(int code, const std::string &msg)
   if (S.abort_on_error) abort();
 }
 
-#define CUDA_OK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fail(100, std::string(#x) + ": " + cudaGetErrorString(e_)); } } while (0)
+// Every check RETURNS from the entry point after fail() (which aborts unless abort_on_error == 0), so a
+// latched error never lets the call run on with a broken precondition.  *_R variants for non-void functions.
+#define CUDA_OK_R(x, ret) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fail(100, std::string(#x) + ": " + cudaGetErrorString(e_)); return ret; } } while (0)
+#define CUDA_OK(x) CUDA_OK_R(x, )
+#define REQUIRE_R(cond, what, ret) do { if (!(cond)) { fail(2, std::string("precondition failed: ") + (what)); return ret; } } while (0)
+#define REQUIRE(cond, what) REQUIRE_R(cond, what, )
 
 template <class T> T *dalloc(size_t n)
 {
   void *p = nullptr;
-  CUDA_OK(cudaMalloc(&p, n * sizeof(T)));
-  CUDA_OK(cudaMemset(p, 0, n * sizeof(T)));
+  CUDA_OK_R(cudaMalloc(&p, n * sizeof(T)), nullptr);
+  CUDA_OK_R(cudaMemset(p, 0, n * sizeof(T)), nullptr);
   S.allocs.push_back(p);
   return (T *)p;
 }
@@ -123,17 +128,16 @@ StatePtrs alloc_state(int nelem, int nlev)
   return s;
 }
 
-void require(bool cond, const char *what)
-{
-  if (!cond) fail(2, std::string("precondition failed: ") + what);
-}
 
 // Errors::check_option equivalents (cxx_f90_interface_theta.cpp:57-73)
-void check_in(const char *name, int v, std::initializer_list<int> ok)
+bool check_in(const char *name, int v, std::initializer_list<int> ok)
 {
-  for (int o : ok) if (o == v) return;
+  for (int o : ok) if (o == v) return true;
   fail(3, std::string("init_simulation_params_c: unsupported value for ") + name + ": " + std::to_string(v));
+  return false;
 }
+#define CHECK_IN(...) do { if (!check_in(__VA_ARGS__)) return; } while (0)
+#define FAIL_IF(cond, code, msg) do { if (cond) { fail(code, msg); return; } } while (0)
 
 }  // namespace
 
@@ -206,6 +210,7 @@ void thetal_b200_get_nccl_id(void *out)
 void thetal_b200_set_abort_on_error(const int *flag) { S.abort_on_error = *flag; }
 int thetal_b200_last_error(void) { return S.last_error; }
 const char *thetal_b200_last_error_msg(void) { return S.last_msg.c_str(); }
+void thetal_b200_clear_error(void) { S.last_error = 0; S.last_msg.clear(); }
 void thetal_b200_set_nlev(const int *nlev)
 {
   if (*nlev < 2 || *nlev > 128) { fail(3, "nlev must be in [2,128]"); return; }
@@ -221,6 +226,9 @@ void thetal_b200_set_extra_params(const int *unused, const int *nlev_tom)
 void init_connectivity(const int *num_local_elems, const int *max_corner_elems)
 {
   S.conns.clear();
+  // one neighbour per corner (uniform cubed sphere); refined meshes list several (dir_idx > 0 in the
+  // reference's convert(), mpi_cxx_f90_interface.cpp:49-60) and would need a list per corner
+  FAIL_IF(*max_corner_elems != 1, 3, "init_connectivity: max_corner_elems != 1 (regionally refined meshes) not supported");
   S.max_corner = *max_corner_elems;
   S.conns.reserve((size_t)*num_local_elems * 8);
 }
@@ -228,7 +236,7 @@ void init_connectivity(const int *num_local_elems, const int *max_corner_elems)
 void add_connection(const int *e1_lid, const int *e1_gid, const int *e1_pos, const int *e1_pid,
                     const int *e2_lid, const int *e2_gid, const int *e2_pos, const int *e2_pid)
 {
-  require(*e1_lid >= 1 && *e1_gid >= 1 && *e1_pos >= 1 && *e1_pid >= 1 && *e2_lid >= 1 && *e2_gid >= 1 &&
+  REQUIRE(*e1_lid >= 1 && *e1_gid >= 1 && *e1_pos >= 1 && *e1_pid >= 1 && *e2_lid >= 1 && *e2_gid >= 1 &&
           *e2_pos >= 1 && *e2_pid >= 1, "add_connection: F90 indices should start at 1");
   Connection c;
   c.e1 = *e1_lid - 1;
@@ -255,7 +263,7 @@ static int corner_point(int dir) { return dir == 4 ? 0 : dir == 5 ? 3 : dir == 6
 void finalize_connectivity(void)
 {
   const int nelem = S.prm.nelem;
-  require(nelem > 0, "init_elements_c must precede finalize_connectivity");
+  REQUIRE(nelem > 0, "init_elements_c must precede finalize_connectivity");
   // ghost slots for neighbours owned by other ranks, numbered in (rank, global id) order
   std::map<std::pair<int, int>, int> ghost;
   for (const Connection &c : S.conns)
@@ -276,7 +284,7 @@ void finalize_connectivity(void)
     const int e2 = remote ? ghost[{c.e2_pid, c.e2_gid}] : c.e2_lid;
     if (remote) lid_of_gid[c.e1_gid] = c.e1;
     if (c.dir1 < 4) {
-      require(c.dir2 < 4, "edge connected to corner");
+      REQUIRE(c.dir2 < 4, "edge connected to corner");
       int p1[4], p2[4];
       edge_points(c.dir1, p1); edge_points(c.dir2, p2);
       // orientation (ConnectivityHelpers.hpp:64-67): same-side pairs and W/N, E/S are reversed
@@ -317,7 +325,7 @@ void finalize_connectivity(void)
       order[4] = 4;
       int n = 0;
       for (int j = 0; j < 5; j++)
-        if (k[order[j]] >= 0) { require(n < 3, "more than 3 DSS neighbours at a point"); S.hdss[((size_t)e * 16 + p) * 3 + n++] = k[order[j]]; }
+        if (k[order[j]] >= 0) { REQUIRE(n < 3, "more than 3 DSS neighbours at a point"); S.hdss[((size_t)e * 16 + p) * 3 + n++] = k[order[j]]; }
     }
   S.h_interior.clear(); S.h_boundary.clear();
   for (int e = 0; e < nelem; e++) {
@@ -349,33 +357,41 @@ void init_simulation_params_c(const int *remap_alg, const int *limiter_option, c
 {
   (void)limiter_option; (void)state_frequency; (void)nu_q; (void)use_moisture;
   (void)disable_diagnostics; (void)use_cpstar; (void)transport_alg; (void)test_case;
-  (void)dt_remap_factor; (void)dt_tracer_factor; (void)nsplit; (void)internal_diagnostics_level;
+  (void)nsplit; (void)internal_diagnostics_level;
   (void)tom_sponge_start;
-  check_in("remap_alg", *remap_alg, {1, 10, 11});                     // PPM only, like cxx_f90_interface_theta.cpp:57-73
+  CHECK_IN("remap_alg", *remap_alg, {1, 10, 11});                     // PPM only, like cxx_f90_interface_theta.cpp:57-73
   S.remap_alg = *remap_alg;
-  check_in("hypervis_order", *hypervis_order, {2});
-  check_in("time_step_type", *time_step_type, {1, 4, 5, 7, 9, 10});
-  check_in("theta_advection_form", *theta_adv_form, {0, 1, 2});
-  check_in("theta_hydrostatic_mode", *theta_hydrostatic_mode, {0});   // NH only (north star)
-  check_in("prescribed_wind", *prescribed_wind, {0});
-  check_in("qsize", *qsize, {0});                                     // tracers out of scope
-  check_in("ftype", *ftype, {-1, 0, 2});
-  check_in("do_3d_turbulence", *do_3d_turbulence, {0});
-  if (!(*nu_p > 0) || !(*nu > 0) || !(*nu_div > 0)) fail(3, "nu, nu_p, nu_div must be > 0");
-  if (!(*dp3d_thresh > 0) || !(*vtheta_thresh > 0)) fail(3, "dp3d_thresh, vtheta_thresh must be > 0");
-  if (*hypervis_scaling != 0.0) fail(3, "tensor hyperviscosity (hypervis_scaling != 0) is a next-row item (SURVEY 8f N4)");
-  if (*laplace_scaling != 0.0) fail(3, "laplace_scaling != 0 not supported");
-  if (*dcmip16_mu != 0.0) fail(3, "dcmip16_mu != 0 not supported");
-  if (*rsplit <= 0) fail(3, "rsplit == 0 (vertically Eulerian) not supported by the CUDA path yet");
+  CHECK_IN("hypervis_order", *hypervis_order, {2});
+  CHECK_IN("time_step_type", *time_step_type, {1, 4, 5, 7, 9, 10});
+  CHECK_IN("theta_advection_form", *theta_adv_form, {0, 1, 2});
+  CHECK_IN("theta_hydrostatic_mode", *theta_hydrostatic_mode, {0});   // NH only (north star)
+  CHECK_IN("prescribed_wind", *prescribed_wind, {0});
+  CHECK_IN("qsize", *qsize, {0});                                     // tracers out of scope
+  CHECK_IN("ftype", *ftype, {-1, 0, 2});
+  CHECK_IN("do_3d_turbulence", *do_3d_turbulence, {0});
+  FAIL_IF(!(*nu_p > 0) || !(*nu > 0) || !(*nu_div > 0), 3, "nu, nu_p, nu_div must be > 0");
+  FAIL_IF(!(*dp3d_thresh > 0) || !(*vtheta_thresh > 0), 3, "dp3d_thresh, vtheta_thresh must be > 0");
+  FAIL_IF(*hypervis_scaling != 0.0, 3, "tensor hyperviscosity (hypervis_scaling != 0) is a next-row item (SURVEY 8f N4)");
+  FAIL_IF(*laplace_scaling != 0.0, 3, "laplace_scaling != 0 not supported");
+  FAIL_IF(*dcmip16_mu != 0.0, 3, "dcmip16_mu != 0 not supported");
+  FAIL_IF(*rsplit <= 0, 3, "rsplit == 0 (vertically Eulerian) not supported by the CUDA path yet");
+  FAIL_IF(*qsplit < 1, 3, "qsplit must be >= 1");
+  FAIL_IF(fabs(*laplacian_rigid_factor * *scale_factor - 1.0) > 1e-12, 3,
+          "planar geometry (laplacian_rigid_factor != 1/scale_factor) not supported");
+  // dt_remap_factor / dt_tracer_factor (prim_driver.cpp:75-88): the dycore-only build has no tracers, so
+  // the only consistent setting is dt_tracer_factor = qsplit, dt_remap_factor = rsplit*qsplit (what
+  // namelist_mod.F90 derives when the namelist gives rsplit/qsplit); <= 0 means "derive it".
+  const int dtf = *dt_tracer_factor > 0 ? *dt_tracer_factor : *qsplit;
+  const int drf = *dt_remap_factor > 0 ? *dt_remap_factor : *rsplit * dtf;
+  FAIL_IF(drf != *rsplit * dtf, 3, "dt_remap_factor must equal rsplit*dt_tracer_factor (independent remap/tracer steps need tracers: out of scope)");
   Params &p = S.prm;
-  p.rsplit = *rsplit; p.qsplit = *qsplit; p.tstep_type = *time_step_type;
+  p.rsplit = *rsplit; p.qsplit = dtf; p.tstep_type = *time_step_type;
   p.theta_advect_form = *theta_adv_form; p.pgrad_correction = *pgrad_correction;
   p.hypervis_subcycle = *hypervis_subcycle; p.hypervis_subcycle_tom = *hypervis_subcycle_tom;
   p.hypervis_scaling_on = 0;
   p.nu = *nu; p.nu_div = *nu_div; p.nu_p = *nu_p; p.nu_s = *nu_s; p.nu_top = *nu_top;
   p.dp3d_thresh = *dp3d_thresh; p.vtheta_thresh = *vtheta_thresh;
   p.rearth_inv = *laplacian_rigid_factor;     // == 1/scale_factor on the sphere (namelist_mod.F90:1045-1047)
-  if (fabs(*laplacian_rigid_factor * *scale_factor - 1.0) > 1e-12) fail(3, "planar geometry (laplacian_rigid_factor != 1/scale_factor) not supported");
   S.hypervis_order = *hypervis_order;
   S.hypervis_scaling = *hypervis_scaling; S.laplace_scaling = *laplace_scaling;
   S.params_set = true;
@@ -383,7 +399,7 @@ void init_simulation_params_c(const int *remap_alg, const int *limiter_option, c
 
 void init_elements_c(const int *nelemd)
 {
-  require(S.nlev > 0, "thetal_b200_set_nlev must precede init_elements_c");
+  REQUIRE(S.nlev > 0, "thetal_b200_set_nlev must precede init_elements_c");
   const int n = *nelemd;
   S.prm.nelem = n; S.prm.nlev = S.nlev;
   S.hD.assign((size_t)n * 64, 0); S.hDinv.assign((size_t)n * 64, 0); S.hmetinv.assign((size_t)n * 64, 0);
@@ -395,7 +411,7 @@ void init_elements_c(const int *nelemd)
 
 void init_hvcoord_c(const double *ps0, thetal_f90ptr hyam, thetal_f90ptr hyai, thetal_f90ptr hybm, thetal_f90ptr hybi)
 {
-  require(S.nlev > 0, "thetal_b200_set_nlev must precede init_hvcoord_c");
+  REQUIRE(S.nlev > 0, "thetal_b200_set_nlev must precede init_hvcoord_c");
   const int n = S.nlev;
   S.hyam.assign(*hyam, *hyam + n); S.hybm.assign(*hybm, *hybm + n);
   S.hyai.assign(*hyai, *hyai + n + 1); S.hybi.assign(*hybi, *hybi + n + 1);
@@ -423,7 +439,7 @@ void init_elements_2d_c(const int *ie, thetal_f90ptr D, thetal_f90ptr Dinv, thet
 {
   (void)sphere_cart_vec; (void)sphere_latlon_vec; (void)tensorvisc2;
   const size_t e = *ie;
-  require((int)e < S.prm.nelem, "init_elements_2d_c: ie out of range");
+  REQUIRE((int)e < S.prm.nelem, "init_elements_2d_c: ie out of range");
   memcpy(&S.hD[e * 64], *D, 64 * sizeof(double));
   memcpy(&S.hDinv[e * 64], *Dinv, 64 * sizeof(double));
   memcpy(&S.hmetinv[e * 64], *metinv, 64 * sizeof(double));
@@ -458,15 +474,15 @@ void init_functors_c(const int *allocate_buffer)
   (void)allocate_buffer;
   if (!S.active) initialize_hommexx_session();
   if (!S.active) return;
-  require(S.params_set, "init_simulation_params_c must precede init_functors_c");
-  require(!S.hyai.empty(), "init_hvcoord_c must precede init_functors_c");
-  require(!S.hdss.empty(), "finalize_connectivity must precede init_functors_c");
+  REQUIRE(S.params_set, "init_simulation_params_c must precede init_functors_c");
+  REQUIRE(!S.hyai.empty(), "init_hvcoord_c must precede init_functors_c");
+  REQUIRE(!S.hdss.empty(), "finalize_connectivity must precede init_functors_c");
   if (S.device_ready) return;
   const int n = S.prm.nelem, nlev = S.nlev;
-  auto up = [&](const std::vector<double> &h) {
+  auto up = [&](const std::vector<double> &h) -> const double * {
     double *d = dalloc<double>(h.size());
-    CUDA_OK(cudaMemcpy(d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
-    return (const double *)d;
+    if (d) CUDA_OK_R(cudaMemcpy(d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice), nullptr);
+    return d;
   };
   S.geo.D = up(S.hD); S.geo.Dinv = up(S.hDinv); S.geo.metinv = up(S.hmetinv);
   S.geo.tensorvisc = up(S.htensorvisc); S.geo.vec_sph2cart = up(S.hvec);
@@ -562,7 +578,7 @@ struct ProfScope {   // per-family device time when thetal_b200_profile_step is 
 // `t`, ncclSend/ncclRecv with every neighbour rank, unpack into the ghost slots of `t`.
 // nk levels of each field (+ w_i(nlevp) when wbot); all on S.stream, so it is ordered between the
 // kernel that produced `t` and the DSS kernel that gathers from it.
-#define NCCL_OK(x) do { ncclResult_t r_ = (x); if (r_ != ncclSuccess) { fail(5, std::string(#x) + ": " + ncclGetErrorString(r_)); } } while (0)
+#define NCCL_OK(x) do { ncclResult_t r_ = (x); if (r_ != ncclSuccess) { fail(5, std::string(#x) + ": " + ncclGetErrorString(r_)); return; } } while (0)
 void halo_exchange(const StatePtrs &t, int nk, int wbot, cudaStream_t st)
 {
   if (S.peers.empty()) return;
@@ -746,7 +762,7 @@ void init_elements_states_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vt
     thetal_f90ptr phinh_i, thetal_f90ptr dp3d, thetal_f90ptr qdp, thetal_f90ptr ps_v)
 {
   (void)qdp; (void)ps_v;
-  require(S.device_ready, "init_functors_c must precede init_elements_states_c");
+  REQUIRE(S.device_ready, "init_functors_c must precede init_elements_states_c");
   if (!S.device_ready) return;
   const size_t nlev = S.nlev;
   double *dv[NTL], *dw[NTL], *dth[NTL], *dphi[NTL], *ddp[NTL];
@@ -764,7 +780,7 @@ void cxx_push_results_to_f90(thetal_f90ptr_out v, thetal_f90ptr_out w_i, thetal_
     thetal_f90ptr_out q, thetal_f90ptr_out omega_p)
 {
   (void)ps_v; (void)qdp; (void)q;
-  require(S.device_ready, "no device state");
+  REQUIRE(S.device_ready, "no device state");
   if (!S.device_ready) return;
   const size_t nlev = S.nlev;
   double *dv[NTL], *dw[NTL], *dth[NTL], *dphi[NTL], *ddp[NTL];
@@ -790,7 +806,7 @@ void push_test_state_to_c(thetal_f90ptr ps_v, thetal_f90ptr dp3d, thetal_f90ptr 
 void init_reference_states_c(thetal_f90ptr theta_ref, thetal_f90ptr dp_ref, thetal_f90ptr phi_ref,
                              thetal_f90ptr nu_scale_top)
 {
-  require(S.device_ready, "init_functors_c must precede init_reference_states_c");
+  REQUIRE(S.device_ready, "init_functors_c must precede init_reference_states_c");
   if (!S.device_ready) return;
   const size_t n = S.prm.nelem, nlev = S.nlev;
   CUDA_OK(cudaMemcpy((void *)S.ref.theta_ref, *theta_ref, n * 16 * nlev * sizeof(double), cudaMemcpyHostToDevice));
@@ -868,7 +884,7 @@ void thetal_b200_halo_stats(long *exchanges, long *bytes) { *exchanges = S.excha
 //   out[0..7] = min ps, max ps, <ps>, <KE>, <PE>, <IE>, <KE+PE+IE>, elements owned by this rank
 void thetal_b200_global_diagnostics(const int *tl, double *out)
 {
-  require(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_global_diagnostics: bad state/time level");
+  REQUIRE(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_global_diagnostics: bad state/time level");
   constexpr int NL = thetal_reprosum::NLIMB, NACC = NDIAG + 2 + NDIAG * NL;
   unsigned long long *maxbits = S.d_diag_acc, *psmm = S.d_diag_acc + NDIAG, *limbs = S.d_diag_acc + NDIAG + 2;
   CUDA_OK(cudaMemsetAsync(S.d_diag_acc, 0, NACC * sizeof(unsigned long long), S.stream));
@@ -910,7 +926,7 @@ static bool tl_ok(int t) { return t >= 0 && t < NTL; }
 void caar_c(const int *np1, const int *nm1, const int *n0, const double *dt2, const double *eta_ave_w,
             const double *scale1, const double *scale2, const double *scale3)
 {
-  require(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "caar_c: bad state/time level");
+  REQUIRE(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "caar_c: bad state/time level");
   run_caar(*np1, *nm1, *n0, *dt2, *eta_ave_w, *scale1, *scale2, *scale3);
   thetal_b200_sync();
 }
@@ -918,7 +934,7 @@ void caar_c(const int *np1, const int *nm1, const int *n0, const double *dt2, co
 void dirk_c(const int *nm1, const double *alphadt_nm1, const int *n0, const double *alphadt_n0,
             const int *np1, const double *dt2, int *itercount, double *itererr)
 {
-  require(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "dirk_c: bad state/time level");
+  REQUIRE(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "dirk_c: bad state/time level");
   CUDA_OK(cudaMemsetAsync(S.d_maxiter, 0, sizeof(int), S.stream));
   CUDA_OK(cudaMemsetAsync(S.d_maxdelta, 0, sizeof(unsigned long long), S.stream));
   run_dirk(*nm1, *alphadt_nm1, *n0, *alphadt_n0, *np1, *dt2);
@@ -930,7 +946,7 @@ void dirk_c(const int *nm1, const double *alphadt_nm1, const int *n0, const doub
 
 void advance_hypervis_c(const int *nt, const double *dt2, const double *eta_ave_w)
 {
-  require(S.device_ready && tl_ok(*nt), "advance_hypervis_c: bad state/time level");
+  REQUIRE(S.device_ready && tl_ok(*nt), "advance_hypervis_c: bad state/time level");
   run_hypervis(*nt, *dt2, *eta_ave_w);
   thetal_b200_sync();
 }
@@ -939,7 +955,7 @@ void prim_advance_exp_c(const double *dt, const int *nm1, const int *n0, const i
                         const int *nstep, const int *compute_diagnostics)
 {
   (void)nstep; (void)compute_diagnostics;
-  require(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "prim_advance_exp_c: bad state/time level");
+  REQUIRE(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "prim_advance_exp_c: bad state/time level");
   run_prim_advance_exp(*dt, *nm1, *n0, *np1);
   thetal_b200_sync();
 }
@@ -954,49 +970,70 @@ static void run_vertical_remap(int np1)
 }
 void vertical_remap_c(const int *np1)
 {
-  require(S.device_ready && tl_ok(*np1), "vertical_remap_c: bad state/time level");
+  REQUIRE(S.device_ready && tl_ok(*np1), "vertical_remap_c: bad state/time level");
   run_vertical_remap(*np1);
   thetal_b200_sync();
 }
 void thetal_b200_set_vertical_remap(const int *on) { S.do_remap = *on; }
 
 // prim_run_subcycle (prim_driver_base.F90:1024-1195, prim_driver.cpp:60-181) restricted to the
-// dynamics: qsize=0, no forcing -- each call advances rsplit*qsplit dynamics steps of length tstep,
-// rotates the time levels (time_mod.F90:109-138) and remaps the result to the reference levels
-// (prim_driver_base.F90:1159: vertical_remap on np1 before the last TimeLevel_update).
+// dynamics (qsize = 0): rsplit x prim_step, each prim_step = zero the derived accumulators
+// (set_tracer_transport_derived_values, prim_step.cpp:24-66) + dt_tracer_factor dynamics steps with
+// a leapfrog time-level update between them; then vertical_remap on np1 (prim_driver.cpp:143-151) and
+// the last TimeLevel update (:170).  nstep, nm1, n0, np1 are pure OUTPUTS, 0-based, taken from the
+// library's own TimeLevel (set by init_time_level_c) exactly as prim_driver.cpp:174-178 does; the
+// Fortran caller passes uninitialised integers and adds 1 afterwards (prim_driver_mod.F90:554-560).
+static void leapfrog_update()
+{ // TimeLevel::update_dynamics_levels(LEAPFROG), time_mod.F90:109-138
+  const int tmp = S.np1; S.np1 = S.nm1; S.nm1 = S.n0; S.n0 = tmp; S.nstep++;
+}
+static void zero_derived_async()
+{
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  cudaMemsetAsync(S.der.vn0, 0, n * 32 * nlev * sizeof(double), S.stream);
+  cudaMemsetAsync(S.der.eta_dot_dpdn, 0, n * 16 * (nlev + 1) * sizeof(double), S.stream);
+  cudaMemsetAsync(S.der.omega_p, 0, n * 16 * nlev * sizeof(double), S.stream);
+}
+static void run_prim_step(double dt)
+{ // prim_step.cpp:68-117
+  zero_derived_async();
+  run_prim_advance_exp(dt, S.nm1, S.n0, S.np1);
+  for (int n = 1; n < S.prm.qsplit; n++) {
+    leapfrog_update();
+    run_prim_advance_exp(dt, S.nm1, S.n0, S.np1);
+  }
+}
 void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int *np1,
                          const int *next_output_step, const int *nsplit_iter)
 {
   (void)next_output_step; (void)nsplit_iter;
-  require(S.device_ready, "prim_run_subcycle_c before init");
-  int t_nm1 = *nm1 - 1, t_n0 = *n0 - 1, t_np1 = *np1 - 1;    // Fortran passes 1-based levels
-  require(tl_ok(t_nm1) && tl_ok(t_n0) && tl_ok(t_np1), "prim_run_subcycle_c: bad time level");
-  // prim_step_type 1 (prim_driver_base.F90:1088-1159): rsplit x prim_step, each prim_step = qsplit dynamics steps
-  const int nsub = (S.prm.rsplit > 0 ? S.prm.rsplit : 1) * (S.prm.qsplit > 0 ? S.prm.qsplit : 1);
-  for (int r = 0; r < nsub; r++) {
-    run_prim_advance_exp(*tstep, t_nm1, t_n0, t_np1);
-    const int tmp = t_np1; t_np1 = t_nm1; t_nm1 = t_n0; t_n0 = tmp;                  // leapfrog update
-    (*nstep)++;
+  REQUIRE(S.device_ready, "prim_run_subcycle_c before init");
+  REQUIRE(tl_ok(S.nm1) && tl_ok(S.n0) && tl_ok(S.np1) && S.nm1 != S.n0 && S.n0 != S.np1 && S.nm1 != S.np1,
+          "prim_run_subcycle_c: init_time_level_c did not set three distinct time levels");
+  run_prim_step(*tstep);
+  for (int r = 1; r < S.prm.rsplit; r++) {
+    leapfrog_update();
+    run_prim_step(*tstep);
   }
-  if (S.do_remap) run_vertical_remap(t_n0);        // the level just computed (np1 before the rotation)
+  if (S.do_remap) run_vertical_remap(S.np1);
   thetal_b200_sync();
-  *nm1 = t_nm1 + 1; *n0 = t_n0 + 1; *np1 = t_np1 + 1;
-  S.nm1 = t_nm1; S.n0 = t_n0; S.np1 = t_np1; S.nstep = *nstep;
+  leapfrog_update();
+  *nstep = S.nstep; *nm1 = S.nm1; *n0 = S.n0; *np1 = S.np1;
 }
 
 double thetal_b200_time_steps(const double *dt, const int *nsteps, int *nm1, int *n0, int *np1)
 {
-  require(S.device_ready, "thetal_b200_time_steps before init");
+  REQUIRE_R(S.device_ready, "thetal_b200_time_steps before init", -1.0);
   int t_nm1 = *nm1, t_n0 = *n0, t_np1 = *np1;
-  CUDA_OK(cudaEventRecord(S.ev0, S.stream));
+  CUDA_OK_R(cudaEventRecord(S.ev0, S.stream), -1.0);
   for (int s = 0; s < *nsteps; s++) {
     run_prim_advance_exp(*dt, t_nm1, t_n0, t_np1);
     const int tmp = t_np1; t_np1 = t_nm1; t_nm1 = t_n0; t_n0 = tmp;
   }
-  CUDA_OK(cudaEventRecord(S.ev1, S.stream));
-  CUDA_OK(cudaEventSynchronize(S.ev1));
+  CUDA_OK_R(cudaEventRecord(S.ev1, S.stream), -1.0);
+  CUDA_OK_R(cudaEventSynchronize(S.ev1), -1.0);
   float ms = 0;
-  CUDA_OK(cudaEventElapsedTime(&ms, S.ev0, S.ev1));
+  CUDA_OK_R(cudaEventElapsedTime(&ms, S.ev0, S.ev1), -1.0);
   *nm1 = t_nm1; *n0 = t_n0; *np1 = t_np1;
   check_device_errors("thetal_b200_time_steps");
   return (double)ms;
@@ -1008,7 +1045,7 @@ namespace { void run_prim_advance_exp(double dt, int nm1, int n0, int np1); }
 extern "C" void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                                          double *ms_by_family, int nfamily)
 {
-  require(S.device_ready, "thetal_b200_profile_step before init");
+  REQUIRE(S.device_ready, "thetal_b200_profile_step before init");
   if (!S.pe0) { CUDA_OK(cudaEventCreate(&S.pe0)); CUDA_OK(cudaEventCreate(&S.pe1)); }
   for (double &m : S.prof_ms) m = 0;
   CUDA_OK(cudaStreamSynchronize(S.stream));
@@ -1023,7 +1060,7 @@ extern "C" void thetal_b200_profile_step(const double *dt, const int *nm1, const
 extern "C" void thetal_b200_push_level(const int *tl, const double *v, const double *w_i, const double *vtheta_dp,
                                        const double *phinh_i, const double *dp3d)
 { // host arrays [ie][k][(c)][16] of ONE time level -> device, asynchronous on the library stream
-  require(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_push_level");
+  REQUIRE(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_push_level");
   const size_t n = S.prm.nelem, nlev = S.nlev;
   const StatePtrs &d = S.tl[*tl];
   CUDA_OK(cudaMemcpyAsync(d.v, v, n * 32 * nlev * sizeof(double), cudaMemcpyHostToDevice, S.stream));
@@ -1035,7 +1072,7 @@ extern "C" void thetal_b200_push_level(const int *tl, const double *v, const dou
 extern "C" void thetal_b200_pull_level(const int *tl, double *v, double *w_i, double *vtheta_dp,
                                        double *phinh_i, double *dp3d)
 {
-  require(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_pull_level");
+  REQUIRE(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_pull_level");
   const size_t n = S.prm.nelem, nlev = S.nlev;
   const StatePtrs &d = S.tl[*tl];
   CUDA_OK(cudaMemcpyAsync(v, d.v, n * 32 * nlev * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
@@ -1097,7 +1134,7 @@ extern "C" void thetal_b200_pipeline_step(const double *dt, const double *v_in, 
     const double *th_in, const double *phi_in, const double *dp_in,
     double *v_out, double *w_out, double *th_out, double *phi_out, double *dp_out)
 {
-  require(S.device_ready, "thetal_b200_pipeline_step before init");
+  REQUIRE(S.device_ready, "thetal_b200_pipeline_step before init");
   if (!S.pipe_ready) pipeline_setup();
   const long j = S.pipe_calls++;
   const int b = (int)(j & 1), e = (int)(j & 3), e3 = (int)((j + 1) & 3);     // e3 = (j-3) mod 4
@@ -1129,6 +1166,6 @@ extern "C" void thetal_b200_pipeline_flush(void)
 // enqueue one dynamics step without synchronising (bench e2e)
 extern "C" void thetal_b200_enqueue_step(const double *dt, const int *nm1, const int *n0, const int *np1)
 {
-  require(S.device_ready, "thetal_b200_enqueue_step before init");
+  REQUIRE(S.device_ready, "thetal_b200_enqueue_step before init");
   run_prim_advance_exp(*dt, *nm1, *n0, *np1);
 }

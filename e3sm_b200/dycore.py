@@ -197,12 +197,18 @@ class ThetaLDycore:
         self.L.prim_advance_exp_c(_cd(dt), _ci(nm1), _ci(n0), _ci(np1), _ci(0), _ci(0))
         self._check()
 
-    def prim_run_subcycle(self, dt, nstep, nm1, n0, np1):
-        """1-based time levels like the Fortran caller; returns updated (nstep, nm1, n0, np1)."""
-        a, b, c, d = c_int(nstep), c_int(nm1), c_int(n0), c_int(np1)
+    def prim_run_subcycle(self, dt):
+        """prim_run_subcycle_c called the way prim_driver_mod.F90:554-560 calls it: the four integers are
+        uninitialised on entry (pure outputs).  Returns (nstep, nm1, n0, np1) as the library's TimeLevel
+        holds them, 0-BASED (the Fortran caller adds 1)."""
+        a, b, c, d = c_int(-12345), c_int(-12345), c_int(-12345), c_int(-12345)
         self.L.prim_run_subcycle_c(_cd(dt), byref(a), byref(b), byref(c), byref(d), _ci(0), _ci(0))
         self._check()
         return a.value, b.value, c.value, d.value
+
+    def init_time_level(self, nm1, n0, np1, nstep=0, nstep0=0):
+        """init_time_level_c with 1-BASED levels like the Fortran caller (prim_driver_mod.F90:196)."""
+        self.L.init_time_level_c(_ci(nm1), _ci(n0), _ci(np1), _ci(nstep), _ci(nstep0))
 
     def vertical_remap(self, np1):
         """vertremap_mod.F90:23-171 on time level np1 (0-based)."""

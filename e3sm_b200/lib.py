@@ -18,7 +18,7 @@ SYMBOLS = [
     "push_forcing_to_c", "prim_run_subcycle_c", "cxx_push_results_to_f90", "push_test_state_to_c",
     "sync_diagnostics_to_host_c",
     "thetal_b200_set_nlev", "thetal_b200_init_comm", "thetal_b200_get_nccl_id",
-    "thetal_b200_set_abort_on_error", "thetal_b200_last_error", "thetal_b200_last_error_msg",
+    "thetal_b200_set_abort_on_error", "thetal_b200_last_error", "thetal_b200_last_error_msg", "thetal_b200_clear_error",
     "thetal_b200_set_extra_params", "prim_advance_exp_c", "caar_c", "dirk_c", "advance_hypervis_c",
     "thetal_b200_get_derived", "thetal_b200_zero_derived", "thetal_b200_sync",
     "thetal_b200_time_steps", "thetal_b200_launch_count", "thetal_b200_profile_step",

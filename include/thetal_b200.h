@@ -82,6 +82,10 @@ void initialize_dp3d_from_ps_c(void);
 /* ---- run time: theta_f2c_mod.F90:189-236; impl H/src/share/cxx/prim_driver.cpp:60-181 */
 void push_forcing_to_c(const double *fm, const double *fvtheta, const double *ft,
                        const double *fphi, const double *fq);
+/* nstep, nm1, n0, np1 are pure OUTPUTS (never read): the library advances its own TimeLevel, set by
+ * init_time_level_c, and reports it 0-BASED as prim_driver.cpp:174-178 does; the Fortran caller adds 1
+ * (prim_driver_mod.F90:554-560).  One call = rsplit prim_steps (each: zero vn0/omega_p/eta_dot_dpdn, then
+ * dt_tracer_factor dynamics steps), vertical_remap, last leapfrog update. */
 void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int *np1,
                          const int *next_output_step, const int *nsplit_iter);
 void cxx_push_results_to_f90(thetal_f90ptr_out v, thetal_f90ptr_out w_i, thetal_f90ptr_out vtheta_dp,
@@ -102,6 +106,7 @@ void thetal_b200_get_nccl_id(void *nccl_id_out);
 void thetal_b200_set_abort_on_error(const int *flag);
 int  thetal_b200_last_error(void);             /* 0 = ok; message via thetal_b200_last_error_msg */
 const char *thetal_b200_last_error_msg(void);
+void thetal_b200_clear_error(void);            /* reset the latched error (abort_on_error == 0 mode) */
 /* extra controls the reference keeps in Fortran modules: control_mod.F90:101-103, model_init_mod */
 void thetal_b200_set_extra_params(const int *hv_ref_profiles_unused, const int *nlev_tom);
 

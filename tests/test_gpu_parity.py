@@ -188,11 +188,9 @@ def test_ten_day_baroclinic_wave_diagnostics(case_c1, remap):
             assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0
     assert o.error_flag == 0
     if remap:
-        nstep, f = 0, (1, 2, 3)
         for _ in range(nsteps // p.rsplit):
-            nstep, *f = d.prim_run_subcycle(p.tstep, nstep, *f)
+            nstep, g_nm1, g_n0, g_np1 = d.prim_run_subcycle(p.tstep)
         assert nstep == nsteps
-        g_n0 = f[1] - 1
     else:
         ms, g_nm1, g_n0, g_np1 = d.time_steps(p.tstep, nsteps, 0, 1, 2)
     assert g_n0 == n0
@@ -317,9 +315,9 @@ def test_prim_run_subcycle_against_committed_fixture(case_c1):
     p, grid, hv, st0, phis, gradphis, refs = case_c1
     d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
     d.set_state(st0.copy())
-    nstep, f_nm1, f_n0, f_np1 = d.prim_run_subcycle(p.tstep, 0, 1, 2, 3)
+    nstep, c_nm1, c_n0, c_np1 = d.prim_run_subcycle(p.tstep)
     sg = d.get_state()
-    _check_against_fixture(sg, f_n0 - 1, global_diagnostics(sg, f_n0 - 1, grid, hv), 1e-9)
+    _check_against_fixture(sg, c_n0, global_diagnostics(sg, c_n0, grid, hv), 1e-9)
     d.close()
 
 
@@ -349,17 +347,64 @@ def test_step_is_bitwise_repeatable():
 
 @pytest.mark.parametrize("qsplit", [1, 2])
 def test_prim_run_subcycle(case_c1, parity_state_c1, qsplit):
-    """the reference entry point: rsplit x qsplit dynamics steps + vertical remap, 1-based time levels in/out"""
+    """The reference entry point called as the Fortran does (prim_driver_mod.F90:554-560): four
+    uninitialised integers in, the library's own 0-based TimeLevel out (prim_driver.cpp:174-178).  Each call =
+    rsplit x prim_step; a prim_step zeroes vn0/omega_p/eta_dot_dpdn (prim_step.cpp:24-66) and runs qsplit
+    dynamics steps; then vertical_remap and the last leapfrog update.  Two calls, so that accumulators that
+    were not reset would show."""
     p, o, so, d = make_pair(case_c1, parity_state_c1.copy(), qsplit=qsplit)
     nm1, n0, np1 = 0, 1, 2
+    for call in range(2):
+        for r in range(p.rsplit):
+            o.vn0[:] = 0; o.omega_p[:] = 0; o.eta_dot_dpdn[:] = 0
+            for q in range(p.qsplit):
+                o.prim_advance_exp(p.tstep, nm1, n0, np1)
+                nm1, n0, np1 = n0, np1, nm1
+        assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0        # prim_driver_base.F90:1159
+        nstep, c_nm1, c_n0, c_np1 = d.prim_run_subcycle(p.tstep)
+        assert nstep == (call + 1) * p.rsplit * p.qsplit and (c_nm1, c_n0, c_np1) == (nm1, n0, np1)
+        # what the Fortran would now hold: tl%n0 = n0_c + 1 etc.
+        assert sorted((c_nm1 + 1, c_n0 + 1, c_np1 + 1)) == [1, 2, 3]
+    assert_state_close(d.get_state(), so, n0, 1e-9, "prim_run_subcycle")
+    vn0, eta, om = d.get_derived()
+    assert rel_l2(vn0, o.vn0) <= 1e-9                                # mean flux over the LAST qsplit steps only
+    assert rel_l2(om, o.omega_p) <= 1e-8
+    d.close()
+
+
+def test_prim_run_subcycle_follows_init_time_level(case_c1, parity_state_c1):
+    """the library advances from the levels init_time_level_c gave it, whatever the integers hold on entry"""
+    p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
+    d.init_time_level(3, 1, 2, nstep=7)          # Fortran 1-based: nm1=3, n0=1, np1=2
+    nm1, n0, np1 = 2, 0, 1
     for _ in range(p.rsplit * p.qsplit):
         o.prim_advance_exp(p.tstep, nm1, n0, np1)
         nm1, n0, np1 = n0, np1, nm1
-    assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0        # prim_driver_base.F90:1159
-    nstep, f_nm1, f_n0, f_np1 = d.prim_run_subcycle(p.tstep, 0, 1, 2, 3)
-    assert nstep == p.rsplit * p.qsplit and (f_nm1 - 1, f_n0 - 1, f_np1 - 1) == (nm1, n0, np1)
-    assert_state_close(d.get_state(), so, n0, 1e-9, "prim_run_subcycle")
+    assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0
+    nstep, c_nm1, c_n0, c_np1 = d.prim_run_subcycle(p.tstep)
+    assert nstep == 7 + p.rsplit * p.qsplit and (c_nm1, c_n0, c_np1) == (nm1, n0, np1)
+    assert_state_close(d.get_state(), so, n0, 1e-9, "prim_run_subcycle from rotated levels")
     d.close()
+
+
+def test_latched_error_returns_before_touching_state(case_c1, parity_state_c1):
+    """abort_on_error = 0: a failed precondition returns from the entry point (no out-of-range time level use)"""
+    import ctypes
+    from e3sm_b200 import lib
+    L = lib.load()
+    L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(0)))
+    try:
+        p, o, so, d = make_pair(case_c1, parity_state_c1.copy())
+        before = d.get_state()
+        with pytest.raises(RuntimeError, match="bad state/time level"):
+            d.compute_andor_apply_rhs(7, 1, 1, 10.0, 0.0, 1.0, 0.0, 1.0)
+        L.thetal_b200_clear_error()
+        after = d.get_state()
+        for f in before.FIELDS:
+            assert np.array_equal(getattr(before, f), getattr(after, f))
+        d.close()
+    finally:
+        L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(1)))
 
 
 def test_limiters_random_state(case_c1):
