@@ -944,6 +944,35 @@ void dirk_c(const int *nm1, const double *alphadt_nm1, const int *n0, const doub
   if (itererr) *itererr = S.max_deltaerr;
 }
 
+// Device time of compute_stage_value_dirk alone (tools/bench_dirk.py): w_i and phinh_i of np1 are saved and
+// restored before every repetition, so each launch solves the same stage problem; returns ms per launch.
+double thetal_b200_time_dirk(const int *nm1, const double *alphadt_nm1, const int *n0, const double *alphadt_n0,
+                             const int *np1, const double *dt2, const int *reps, int *itercount)
+{
+  REQUIRE_R(S.device_ready && tl_ok(*np1) && tl_ok(*nm1) && tl_ok(*n0), "thetal_b200_time_dirk: bad state/time level", -1.0);
+  const size_t bytes = (size_t)S.prm.nelem * 16 * (S.nlev + 1) * sizeof(double);
+  const StatePtrs &st = S.tl[*np1];
+  CUDA_OK_R(cudaMemcpyAsync(S.tensB.w, st.w, bytes, cudaMemcpyDeviceToDevice, S.stream), -1.0);
+  CUDA_OK_R(cudaMemcpyAsync(S.tensB.phi, st.phi, bytes, cudaMemcpyDeviceToDevice, S.stream), -1.0);
+  CUDA_OK_R(cudaMemsetAsync(S.d_maxiter, 0, sizeof(int), S.stream), -1.0);
+  double total = 0;
+  for (int r = 0; r < *reps; r++) {
+    CUDA_OK_R(cudaMemcpyAsync(st.w, S.tensB.w, bytes, cudaMemcpyDeviceToDevice, S.stream), -1.0);
+    CUDA_OK_R(cudaMemcpyAsync(st.phi, S.tensB.phi, bytes, cudaMemcpyDeviceToDevice, S.stream), -1.0);
+    CUDA_OK_R(cudaEventRecord(S.ev0, S.stream), -1.0);
+    run_dirk(*nm1, *alphadt_nm1, *n0, *alphadt_n0, *np1, *dt2);
+    CUDA_OK_R(cudaEventRecord(S.ev1, S.stream), -1.0);
+    CUDA_OK_R(cudaEventSynchronize(S.ev1), -1.0);
+    float ms = 0;
+    CUDA_OK_R(cudaEventElapsedTime(&ms, S.ev0, S.ev1), -1.0);
+    total += ms;
+  }
+  sync_diagnostics_to_host_c();
+  if (itercount) *itercount = S.max_itercnt;
+  check_device_errors("thetal_b200_time_dirk");
+  return total / (*reps > 0 ? *reps : 1);
+}
+
 void advance_hypervis_c(const int *nt, const double *dt2, const double *eta_ave_w)
 {
   REQUIRE(S.device_ready && tl_ok(*nt), "advance_hypervis_c: bad state/time level");

@@ -1,0 +1,512 @@
+// compute_stage_value_dirk (IM:60-364), column-parallel form: TPC lanes of one warp own one column
+// (TPC = 16: a half-warp per column, 256 threads per element; TPC = 32: a warp per column, 512 threads),
+// lane j holds the ITEMS consecutive levels k = j*ITEMS .. j*ITEMS+ITEMS-1 in registers.  Everything a
+// level needs from its vertical neighbours is either in the same thread or one warp shuffle away, so the
+// Newton iteration has no shared-memory traffic and ONE block barrier (the per-element convergence test
+// of IM:330-335).  The tridiagonal system J x = -F (IM:414-433, 576-599) is solved without a serial
+// sweep over the column:
+//   1. every lane eliminates its own ITEMS rows (partition method: forward elimination of the
+//      sub-diagonal, backward elimination of the super-diagonal) down to one equation that couples the
+//      last unknown of the lane to the last unknowns of the two neighbouring lanes;
+//   2. the TPC reduced equations of a column are solved by parallel cyclic reduction with warp shuffles
+//      (log2 TPC rounds, rows kept normalised so a round costs one reciprocal);
+//   3. every lane back-substitutes its interior unknowns (two FMAs per row).
+// Levels beyond nlev (the column is padded to TPC*ITEMS rows) are identity rows behind the last real
+// row, whose super-diagonal is zero, so they never couple to anything.
+// Included by thetal_kernels.cu inside namespace thetal (uses its constants and helpers).
+#pragma once
+
+constexpr unsigned FULLMASK = 0xffffffffu;
+
+// sum of v over the lanes below / above this one inside the TPC-lane column group
+template <int TPC>
+__device__ __forceinline__ double excl_sum_below(double v, int j)
+{
+  double e = __shfl_up_sync(FULLMASK, v, 1, TPC);
+  if (j == 0) e = 0.0;
+#pragma unroll
+  for (int s = 1; s < TPC; s <<= 1) {
+    const double t = __shfl_up_sync(FULLMASK, e, s, TPC);
+    if (j >= s) e = e + t;
+  }
+  return e;
+}
+template <int TPC>
+__device__ __forceinline__ double excl_sum_above(double v, int j)
+{
+  double e = __shfl_down_sync(FULLMASK, v, 1, TPC);
+  if (j == TPC - 1) e = 0.0;
+#pragma unroll
+  for (int s = 1; s < TPC; s <<= 1) {
+    const double t = __shfl_down_sync(FULLMASK, e, s, TPC);
+    if (j + s < TPC) e = e + t;
+  }
+  return e;
+}
+template <int TPC>
+__device__ __forceinline__ double group_max(double v)
+{
+#pragma unroll
+  for (int s = 1; s < TPC; s <<= 1) v = fmax(v, __shfl_xor_sync(FULLMASK, v, s, TPC));
+  return v;
+}
+template <int TPC>
+__device__ __forceinline__ double group_min(double v)
+{
+#pragma unroll
+  for (int s = 1; s < TPC; s <<= 1) v = fmin(v, __shfl_xor_sync(FULLMASK, v, s, TPC));
+  return v;
+}
+
+// x / 1e5 to <= 1 ulp without a reciprocal instruction (P0 is a constant)
+__device__ __forceinline__ double div_p0(double x)
+{
+  constexpr double c = 1.0 / P0;
+  const double q = x * c;
+  const double rem = fma(-q, P0, x);
+  return fma(rem, c, q);
+}
+
+// IM:42-53 at one interface from the two adjacent levels
+__device__ __forceinline__ double gwphis_of(double dk, double dm, double v1k, double v1m, double v2k, double v2m,
+                                            double g1, double g2, double hyb)
+{
+  const double r = rcp46(dk + dm);
+  const double n1 = dk * v1k + dm * v1m, n2 = dk * v2k + dm * v2m;
+  double q1 = n1 * r, q2 = n2 * r;
+  q1 = fma(fma(-q1, dk + dm, n1), r, q1);
+  q2 = fma(fma(-q2, dk + dm, n2), r, q2);
+  return (q1 * g1 + q2 * g2) * hyb;
+}
+
+// EOS of one level from dphi (EOS:175-183): pnh and c = pnh/dphi (IM:417) with one reciprocal
+__device__ __forceinline__ void eos_level(double rth, double dphi, double &pnh, double &c)
+{
+  const double r = rcp46(dphi);                       // 1/dphi (< 0)
+  const double q0 = -(rth * r);
+  const double poe = fma(fma(q0, dphi, rth), -r, q0); // Rgas*vtheta_dp/(-dphi), <= 1 ulp
+  pnh = P0 * thetal_pow::pow_pos(div_p0(poe), C_GAMMA);
+  c = pnh * r;
+}
+
+template <int ITEMS, int TPC>
+struct DirkColCfg {
+  static constexpr int NT = 16 * TPC;
+  // Shared memory: (a) per-thread private arrays w0, dphi0, phi0 ([slot][thread], conflict-free);
+  // (b) the staging area of ONE element's columns, transposed to [field][point][level] with an odd row
+  // pitch SS: filled by coalesced 8-byte cp.async (a warp copies 256 contiguous bytes of the [level][point]
+  // global layout per instruction), read by each thread along its own column without bank conflicts
+  // (ITEMS = 5: lane stride 5 doubles).  Six fields: th, dp, w, phi, v1, v2.
+  static constexpr int SS = (ITEMS * TPC + 1) | 1;              // >= nlevp, odd
+  static constexpr size_t priv_doubles = 3 * ITEMS * NT, stage_doubles = 6 * 16 * (size_t)SS;
+  static constexpr size_t smem_bytes = sizeof(double) * (priv_doubles + stage_doubles);
+  static constexpr int minb = (2 * (smem_bytes + 2304) <= 232448) ? 2 : 1;   // CTAs per SM that fit in 227 KB
+};
+
+__device__ __forceinline__ void cp_async8(double *dst, const double *src)
+{
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <int ITEMS, int TPC>
+__global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk_col_kernel(const DirkArgs A)
+{
+  constexpr int NT = 16 * TPC, NW = NT / 32, M = ITEMS;
+  static_assert(ITEMS >= 2, "the partition solve needs two rows per lane");
+  extern __shared__ double smem[];
+  __shared__ double red[3][NW];
+  __shared__ int sflag;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, n16 = 16 * nlev, nelem = A.prm.nelem;
+  const int tid = threadIdx.x, j = tid % TPC, p = tid / TPC, k0 = j * ITEMS;
+  double *s_w0 = smem + tid, *s_dphi0 = smem + ITEMS * NT + tid, *s_phi0 = smem + 2 * ITEMS * NT + tid;
+  const double g = G_GRAV, dt2 = A.dt2, dtg = dt2 * g, ptop = A.prm.ptop;
+  const int km = min(max(k0 - 1, 0), nlev - 1);
+  using Cfg = DirkColCfg<ITEMS, TPC>;
+  constexpr int SS = Cfg::SS;
+  double *st_th = smem + Cfg::priv_doubles, *st_dp = st_th + 16 * SS, *st_w = st_dp + 16 * SS;
+  double *st_phi = st_w + 16 * SS, *st_v1 = st_phi + 16 * SS, *st_v2 = st_v1 + 16 * SS;
+  // The CTAs are persistent (grid = CTAs resident on the chip, elements strided over them).  While one
+  // element iterates, the np1 columns of the CTA's next element travel into the staging area with
+  // cp.async, and the n0/nm1 columns the explicit terms need go to L2.
+  auto stage_state = [&](const StatePtrs &S, int e) {
+    const double *eth = S.th + (size_t)e * n16, *edp = S.dp + (size_t)e * n16, *ev = S.v + (size_t)e * 2 * n16;
+    const double *ew = S.w + (size_t)e * 16 * nlevp, *ephi = S.phi + (size_t)e * 16 * nlevp;
+    for (int q = tid; q < n16; q += NT) {
+      const int o = (q & 15) * SS + (q >> 4);
+      cp_async8(st_th + o, eth + q);
+      cp_async8(st_dp + o, edp + q);
+    }
+    for (int q = tid; q < 16 * nlevp; q += NT) {
+      const int o = (q & 15) * SS + (q >> 4);
+      cp_async8(st_w + o, ew + q);
+      cp_async8(st_phi + o, ephi + q);
+    }
+    for (int q = tid; q < 2 * n16; q += NT) {
+      const int o = (q & 15) * SS + (q >> 5);
+      cp_async8(((q & 16) ? st_v2 : st_v1) + o, ev + q);
+    }
+    cp_async_commit();
+  };
+  auto prefetch_explicit = [&](int e) {
+    if (tid < 10) {
+      const StatePtrs &S = tid < 5 ? A.n0 : A.nm1;
+      const bool on = tid < 5 ? A.alphadt_n0 != 0.0 : A.alphadt_nm1 != 0.0;
+      const int f = tid % 5;
+      const unsigned bv = 32u * nlev * 8u, bm = 16u * nlev * 8u, bi = 16u * nlevp * 8u;
+      if (on) {
+        if (f == 0) prefetch_l2(S.dp + (size_t)e * n16, bm);
+        if (f == 1) prefetch_l2(S.th + (size_t)e * n16, bm);
+        if (f == 2) prefetch_l2(S.w + (size_t)e * 16 * nlevp, bi);
+        if (f == 3) prefetch_l2(S.phi + (size_t)e * 16 * nlevp, bi);
+        if (f == 4) prefetch_l2(S.v + (size_t)e * 2 * n16, bv);
+      }
+    }
+  };
+  const double *cth = st_th + p * SS, *cdp = st_dp + p * SS, *cw = st_w + p * SS, *cphi = st_phi + p * SS;
+  const double *cv1 = st_v1 + p * SS, *cv2 = st_v2 + p * SS;       // this thread's column in the staging area
+
+  int ie = blockIdx.x;
+  if (ie < nelem) { stage_state(A.np1, ie); prefetch_explicit(ie); }
+  int bad = 0;
+  for (; ie < nelem; ie += gridDim.x) {
+  double *gw = A.np1.w + (size_t)ie * 16 * nlevp, *gphi = A.np1.phi + (size_t)ie * 16 * nlevp;
+  const double gp1 = A.geo.gradphis[(size_t)ie * 32 + p], gp2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
+  const int ie_next = ie + (int)gridDim.x;
+  if (tid == 0) sflag = 0;
+  if (ie_next < nelem) prefetch_explicit(ie_next);
+
+  double w[ITEMS], dphi[ITEMS], rdpi[ITEMS], rth[ITEMS];
+  double dp[ITEMS], w0[ITEMS], phi0[ITEMS], v1[ITEMS], v2[ITEMS];
+  cp_async_wait_all();
+  __syncthreads();
+  // ---- the column slice, wmax (IM:168-170) ----
+  double wmax = 0.0;
+  const double dpm0 = cdp[km], v1m0 = cv1[km], v2m0 = cv2[km];   // level above the slice
+  const double wbot = cw[nlev];
+  const double phis = cphi[nlev];                             // phinh_i(nlevp) = phis, never changed
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const int k = k0 + i, kk = min(k, nlev - 1);
+    const bool valid = k < nlev;
+    const double th = cth[kk];
+    dp[i] = cdp[kk]; phi0[i] = cphi[kk]; v1[i] = cv1[kk]; v2[i] = cv2[kk];
+    if (valid && (th < 0 || dp[i] < 0)) bad = 1;
+    const double dpi = (k > 0) ? (dp[i] + (i > 0 ? dp[i > 0 ? i - 1 : 0] : dpm0)) / 2 : dp[i];
+    rdpi[i] = div_fast(1.0, dpi);
+    rth[i] = RGAS * th;
+    w0[i] = valid ? cw[kk] : 0.0;
+    wmax = fmax(wmax, fabs(w0[i]));
+  }
+  if (j == TPC - 1) wmax = fmax(wmax, fabs(wbot));
+  wmax = group_max<32>(wmax);
+  if ((tid & 31) == 0) red[2][tid >> 5] = wmax;
+  __syncthreads();
+  wmax = red[2][0];
+#pragma unroll
+  for (int i = 1; i < NW; i++) wmax = fmax(wmax, red[2][i]);
+  wmax = fmax(1.0, wmax);
+
+  // ---- explicit stiff terms of earlier stages (IM:176-205): the n0 / nm1 columns of this element pass
+  // through the staging area (every thread has read its np1 slice before the barrier above) ----
+  for (int pass = 0; pass < 2; pass++) {
+    const double dt3 = pass == 0 ? A.alphadt_n0 : A.alphadt_nm1;
+    if (dt3 == 0.0) continue;
+    if (pass == 1) __syncthreads();                    // pass 0 has been read by everybody
+    stage_state(pass == 0 ? A.n0 : A.nm1, ie);
+    cp_async_wait_all();
+    __syncthreads();
+    double tp[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const int k = k0 + i, kk = min(k, nlev - 1);
+      const double dph = cphi[kk + 1] - cphi[kk], th = cth[kk], tdpk = cdp[kk];
+      if (k < nlev && (th < 0 || tdpk < 0 || dph > 0)) bad = 1;
+      tp[i] = eos_pnh(div_fast(RGAS * th, -dph));
+    }
+    const double tpm = __shfl_up_sync(FULLMASK, tp[ITEMS - 1], 1, TPC);
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const int k = k0 + i, kk = min(k, nlev - 1), kq = max(kk - 1, 0);
+      const double dk = cdp[kk], dm = cdp[kq];
+      double mu;
+      if (k == 0) mu = div_fast(2 * (tp[i] - ptop), dk);
+      else mu = div_fast(tp[i] - (i > 0 ? tp[i > 0 ? i - 1 : 0] : tpm), (dk + dm) / 2);
+      w0[i] = w0[i] + dt3 * g * (mu - 1);
+      const double gwh = (k == 0) ? 0.0 : gwphis_of(dk, dm, cv1[kk], cv1[kq], cv2[kk], cv2[kq], gp1, gp2, c_hybi[kk]);
+      phi0[i] = phi0[i] + dt3 * g * cw[kk] - dt3 * gwh;
+    }
+  }
+  // the staging area is consumed: fetch the next element of this CTA behind the Newton iterations
+  if (ie_next < nelem) {
+    if (A.alphadt_n0 != 0.0 || A.alphadt_nm1 != 0.0) __syncthreads();
+    stage_state(A.np1, ie_next);
+  }
+  // ---- wphis(np1) term (IM:208-211) ----
+  {
+    double v1m = v1m0, v2m = v2m0, dm = dpm0;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const int k = k0 + i, kk = min(k, nlev - 1);
+      const double v1k = v1[i], v2k = v2[i];
+      const double gwh = (k == 0) ? 0.0 : gwphis_of(dp[i], dm, v1k, v1m, v2k, v2m, gp1, gp2, c_hybi[kk]);
+      phi0[i] = phi0[i] - dt2 * gwh;
+      v1m = v1k; v2m = v2k; dm = dp[i];
+    }
+  }
+  // ---- hydrostatic initial guess phi_from_eos (EOS:286-302, IM:228-230) ----
+  // running sums as (sum inside the lane) + (sum over the lanes above/below): the guess only starts Newton
+  {
+    double acc = 0.0, pin[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) { pin[i] = acc; acc = acc + ((k0 + i < nlev) ? dp[i] : 0.0); }
+    const double ptl = ptop + excl_sum_below<TPC>(acc, j);          // pressure at the top interface of the slice
+    double term[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const double pi_k = ptl + pin[i], pn = pi_k + dp[i];
+      const double pmid = (pn + pi_k) / 2;
+      const double t = div_p0(rth[i] * thetal_pow::pow_pos(div_p0(pmid), C_KM1));
+      term[i] = (k0 + i < nlev) ? t : 0.0;
+    }
+    // phi_k = phis + sum_{k' >= k} term_k'
+    double suf[ITEMS];
+    acc = 0.0;
+#pragma unroll
+    for (int i = ITEMS - 1; i >= 0; i--) { acc = acc + term[i]; suf[i] = acc; }
+    const double below = phis + excl_sum_above<TPC>(acc, j);        // phi at the bottom interface of the slice
+    double ph[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) ph[i] = below + suf[i];
+    const double ph_next = __shfl_down_sync(FULLMASK, ph[0], 1, TPC);       // first level of the lane below
+    const double p0_next = __shfl_down_sync(FULLMASK, phi0[0], 1, TPC);
+    int nsafe = 0;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {                                               // IM:234-253
+      const int k = k0 + i;
+      const bool lastlev = (k == nlev - 1), inlane = (i + 1 < ITEMS);
+      const double phb = lastlev ? phis : (inlane ? ph[inlane ? i + 1 : i] : ph_next);
+      const double p0b = lastlev ? phis : (inlane ? phi0[inlane ? i + 1 : i] : p0_next);
+      double d = phb - ph[i];
+      s_dphi0[i * NT] = p0b - phi0[i];
+      if (k < nlev && d > -g) { d = -g; nsafe = 1; }
+      dphi[i] = (k < nlev) ? d : -g;                          // padded rows: any harmless negative value
+    }
+    if (nsafe) sflag = 1;
+    __syncthreads();
+    if (sflag) {                                                                    // IM:254-260 (rare, whole element)
+      acc = 0.0;
+#pragma unroll
+      for (int i = ITEMS - 1; i >= 0; i--) { acc = acc - ((k0 + i < nlev) ? dphi[i] : 0.0); suf[i] = acc; }
+      const double below2 = phis + excl_sum_above<TPC>(acc, j);
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) ph[i] = below2 + suf[i];
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      w[i] = (k0 + i < nlev) ? div_fast(ph[i] - phi0[i], dtg) : 0.0;
+      s_w0[i * NT] = w0[i];
+      s_phi0[i * NT] = phi0[i];
+    }
+  }
+  double pnh[ITEMS], cc[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    if (k0 + i < nlev && dphi[i] > 0) bad = 1;
+    eos_level(rth[i], dphi[i], pnh[i], cc[i]);                                      // IM:261
+  }
+
+  // ---- Newton iteration (IM:268-336) ----
+  int itercount = 0;
+  double deltaerr = 0.0;
+  const int maxiter = 20;
+  const double ajac = dtg * dtg / (1 - KAPPA);                                      // IM:414
+  while (itercount < maxiter) {
+    // rows of J x = -F for this lane's levels (IM:414-433, 263-264)
+    double sub[ITEMS], dg[ITEMS], sup[ITEMS], rhs[ITEMS];
+    {
+      double pm = __shfl_up_sync(FULLMASK, pnh[ITEMS - 1], 1, TPC);
+      double cm = __shfl_up_sync(FULLMASK, cc[ITEMS - 1], 1, TPC);
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) {
+        const int k = k0 + i;
+        const bool first = (k == 0), last = (k == nlev - 1), valid = (k < nlev);
+        const double bk = ajac * rdpi[i];
+        const double mu = ((first ? 2.0 : 1.0) * (pnh[i] - (first ? ptop : pm))) * rdpi[i];
+        const double Fn = w[i] - (s_w0[i * NT] + dtg * (mu - 1));
+        const double lo = first ? 0.0 : bk * cm;
+        const double up = (first ? 2.0 : 1.0) * (bk * cc[i]);
+        sub[i] = valid ? lo : 0.0;
+        dg[i] = valid ? (1 - lo - up) : 1.0;
+        sup[i] = (valid && !last) ? up : 0.0;
+        rhs[i] = valid ? -Fn : 0.0;
+        pm = pnh[i]; cm = cc[i];
+      }
+    }
+    // 1. forward elimination inside the lane: row i becomes  f_i s_prev + dg_i x_i + sup_i x_{i+1} = rhs_i
+    double f[ITEMS], rinv[ITEMS - 1], gq[ITEMS - 1];
+    f[0] = sub[0];
+#pragma unroll
+    for (int i = 1; i < M; i++) {
+      rinv[i - 1] = rcp46(dg[i - 1]);
+      const double l = sub[i] * rinv[i - 1];
+      dg[i] = fma(-l, sup[i - 1], dg[i]);
+      rhs[i] = fma(-l, rhs[i - 1], rhs[i]);
+      f[i] = -(l * f[i - 1]);
+    }
+    //    backward elimination: rows i <= M-2 become  f_i s_prev + dg_i x_i + gq_i s_own = rhs_i
+    gq[M - 2] = sup[M - 2];
+#pragma unroll
+    for (int i = M - 3; i >= 0; i--) {
+      const double t = sup[i] * rinv[i + 1];
+      f[i] = fma(-t, f[i + 1], f[i]);
+      gq[i] = -(t * gq[i + 1]);
+      rhs[i] = fma(-t, rhs[i + 1], rhs[i]);
+    }
+    // 2. reduced equation of the lane: the first row of the lane below removes x_{first of next lane}
+    double Ar, Cr, Rr;
+    {
+      const double F0 = f[0] * rinv[0], G0 = gq[0] * rinv[0], R0 = rhs[0] * rinv[0];
+      const double Fd = __shfl_down_sync(FULLMASK, F0, 1, TPC);
+      const double Gd = __shfl_down_sync(FULLMASK, G0, 1, TPC);
+      const double Rd = __shfl_down_sync(FULLMASK, R0, 1, TPC);
+      const double cl = sup[M - 1];                   // zero in the last lane (last level or padding)
+      const double D = fma(-cl, Fd, dg[M - 1]);
+      const double rD = rcp46(D);
+      Ar = f[M - 1] * rD;
+      Cr = -(cl * Gd) * rD;
+      Rr = fma(-cl, Rd, rhs[M - 1]) * rD;
+    }
+    //    parallel cyclic reduction over the TPC lanes of the column, rows normalised to unit diagonal
+#pragma unroll
+    for (int s = 1; s < TPC; s <<= 1) {
+      double Au = __shfl_up_sync(FULLMASK, Ar, s, TPC), Cu = __shfl_up_sync(FULLMASK, Cr, s, TPC);
+      double Ru = __shfl_up_sync(FULLMASK, Rr, s, TPC);
+      double Ad = __shfl_down_sync(FULLMASK, Ar, s, TPC), Cd = __shfl_down_sync(FULLMASK, Cr, s, TPC);
+      double Rd = __shfl_down_sync(FULLMASK, Rr, s, TPC);
+      if (j < s) { Au = 0.0; Cu = 0.0; Ru = 0.0; }
+      if (j + s >= TPC) { Ad = 0.0; Cd = 0.0; Rd = 0.0; }
+      const double Dn = fma(-Cr, Ad, fma(-Ar, Cu, 1.0));
+      const double rD = rcp46(Dn);
+      Rr = fma(-Cr, Rd, fma(-Ar, Ru, Rr)) * rD;
+      if (2 * s < TPC) {
+        const double An = -(Ar * Au) * rD, Cn = -(Cr * Cd) * rD;
+        Ar = An; Cr = Cn;
+      }
+    }
+    // 3. back-substitution inside the lane
+    double x[ITEMS];
+    x[M - 1] = Rr;
+    {
+      double sp = __shfl_up_sync(FULLMASK, Rr, 1, TPC);
+      if (j == 0) sp = 0.0;
+#pragma unroll
+      for (int i = 0; i < M - 1; i++) x[i] = fma(-gq[i], Rr, fma(-f[i], sp, rhs[i])) * rinv[i];
+    }
+    // dphi update (IM:278-283), positivity check, w update (IM:320-322)
+    const double x_next = __shfl_down_sync(FULLMASK, x[0], 1, TPC);
+    const double w_next = __shfl_down_sync(FULLMASK, w[0], 1, TPC);
+    int anypos = 0;
+    double xmax = 0.0;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const int k = k0 + i;
+      const bool inlane = (i + 1 < ITEMS);
+      const double xb = inlane ? x[inlane ? i + 1 : i] : x_next, wb = inlane ? w[inlane ? i + 1 : i] : w_next;
+      double d;
+      if (k < nlev - 1) d = s_dphi0[i * NT] + dtg * ((wb - w[i]) + (xb - x[i]));
+      else d = s_dphi0[i * NT] - dtg * (w[i] + x[i]);
+      if (k < nlev) { dphi[i] = d; if (d >= 0) anypos = 1; }
+      xmax = fmax(xmax, fabs(x[i]));
+    }
+    double alpha = 1.0;
+    if (__any_sync(FULLMASK, anypos)) {                                             // IM:285-319 (rare), per column
+      const unsigned bal = __ballot_sync(FULLMASK, anypos);
+      const unsigned gmask = (TPC == 32) ? FULLMASK : (0xffffu << ((tid & 16)));
+      const bool colpos = (bal & gmask) != 0;
+      double amin = 1.0;
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) {
+        const int k = k0 + i;
+        const bool inlane = (i + 1 < ITEMS);
+        const double xb = inlane ? x[inlane ? i + 1 : i] : x_next, wb = inlane ? w[inlane ? i + 1 : i] : w_next;
+        double dx, dw;
+        if (k < nlev - 1) { dx = xb - x[i]; dw = wb - w[i]; }
+        else { dx = -x[i]; dw = -w[i]; }
+        if (k < nlev && dx != 0) {
+          const double alpha_k = -(s_dphi0[i * NT] + dtg * dw) / (dtg * dx);
+          if (alpha_k >= 0) amin = fmin(amin, alpha_k);
+        }
+      }
+      amin = group_min<TPC>(amin);
+      if (colpos) {
+        alpha = amin / 2;
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+          const int k = k0 + i;
+          const bool inlane = (i + 1 < ITEMS);
+          const double xb = inlane ? x[inlane ? i + 1 : i] : x_next, wb = inlane ? w[inlane ? i + 1 : i] : w_next;
+          double d;
+          if (k < nlev - 1) d = s_dphi0[i * NT] + dtg * ((wb - w[i]) + alpha * (xb - x[i]));
+          else d = s_dphi0[i * NT] - dtg * (w[i] + alpha * x[i]);
+          if (k < nlev) dphi[i] = d;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) w[i] = w[i] + alpha * x[i];
+    // per-element convergence test (IM:330-335): one barrier, double-buffered partial maxima
+    xmax = group_max<32>(xmax);
+    double *rb = red[itercount & 1];
+    if ((tid & 31) == 0) rb[tid >> 5] = xmax;
+    __syncthreads();
+    xmax = rb[0];
+#pragma unroll
+    for (int i = 1; i < NW; i++) xmax = fmax(xmax, rb[i]);
+    deltaerr = div_fast(xmax, wmax);                                                // IM:330
+    itercount++;
+    if (deltaerr < 1.0e-11) break;                                                  // IM:335
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      if (k0 + i < nlev && dphi[i] > 0) bad = 1;
+      eos_level(rth[i], dphi[i], pnh[i], cc[i]);                                    // IM:324
+    }
+  }
+  // ---- phi update (IM:339) and write back ----
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const int k = k0 + i, q = k * 16 + p;
+    if (k < nlev) {
+      gw[q] = w[i];
+      gphi[q] = s_phi0[i * NT] + dtg * w[i];
+    }
+  }
+  if (tid == 0) {
+    atomicMax(A.max_iter, itercount);
+    atomicMax(A.max_deltaerr_bits, (unsigned long long)__double_as_longlong(deltaerr));
+    if (itercount >= maxiter) atomicOr(A.err, ERR_DIRK_NOT_CONVERGED);
+  }
+  }   // element loop
+  if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
+}
+
+template <int ITEMS, int TPC>
+static void launch_dirk_col_t(const DirkArgs &A, cudaStream_t st)
+{
+  using Cfg = DirkColCfg<ITEMS, TPC>;
+  static int grid_cap = 0;
+  if (!grid_cap) {
+    cudaFuncSetAttribute(dirk_col_kernel<ITEMS, TPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    int dev = 0, nsm = 148, per_sm = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dirk_col_kernel<ITEMS, TPC>, Cfg::NT, Cfg::smem_bytes);
+    grid_cap = nsm * (per_sm > 0 ? per_sm : 1);      // persistent: every CTA resident, elements strided over them
+  }
+  static const int grid_env = [] { const char *e = getenv("THETAL_B200_DIRK_GRID"); return e ? atoi(e) : -1; }();
+  int grid = A.prm.nelem < grid_cap ? A.prm.nelem : grid_cap;
+  if (grid_env == 0) grid = A.prm.nelem;                       // tuning: one element per CTA
+  else if (grid_env > 0 && grid_env < A.prm.nelem) grid = grid_env;
+  dirk_col_kernel<ITEMS, TPC><<<grid, Cfg::NT, Cfg::smem_bytes, st>>>(A);
+}

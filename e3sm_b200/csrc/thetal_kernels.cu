@@ -14,6 +14,7 @@
 #include "thetal_pow.h"
 #include "thetal_reprosum.h"
 #include <cstdio>
+#include <cstdlib>
 
 namespace thetal {
 
@@ -978,8 +979,25 @@ static void launch_dirk_t(const DirkArgs &A, cudaStream_t st, size_t sm)
   dirk_kernel<ITEMS><<<A.prm.nelem, DIRK_THREADS, sm, st>>>(A);
 }
 
+}  // namespace thetal
+namespace thetal {
+#include "thetal_dirk_col.cuh"
+
 void launch_dirk(const DirkArgs &A, cudaStream_t st)
 {
+  static const int variant = [] { const char *e = getenv("THETAL_B200_DIRK"); return e ? atoi(e) : 1; }();
+  if (variant == 1) {       // column-parallel solve (half-warp per column, partition + cyclic reduction)
+    switch ((A.prm.nlev + 15) / 16) {
+      case 0: case 1: case 2: launch_dirk_col_t<2, 16>(A, st); break;
+      case 3: launch_dirk_col_t<3, 16>(A, st); break;
+      case 4: launch_dirk_col_t<4, 16>(A, st); break;
+      case 5: launch_dirk_col_t<5, 16>(A, st); break;
+      case 6: launch_dirk_col_t<6, 16>(A, st); break;
+      case 7: launch_dirk_col_t<7, 16>(A, st); break;
+      default: launch_dirk_col_t<8, 16>(A, st); break;
+    }
+    return;
+  }
   const size_t sm = dirk_smem_bytes(A.prm.nlev);
   const int need = (16 * A.prm.nlev + DIRK_THREADS - 1) / DIRK_THREADS;
   if (need <= 2) launch_dirk_t<2>(A, st, sm);

@@ -104,7 +104,7 @@ class ThetaLDycore:
             _cd(p.hypervis_scaling), _cd(0.0), _cd(0.0),
             _ci(-1), _ci(p.theta_advect_form), _ci(0), _ci(0), _ci(1), _ci(0),
             _ci(0), _ci(0), byref(name),
-            _ci(p.rsplit), _ci(p.qsplit), _cd(grid.rearth), _cd(1.0 / grid.rearth), _ci(1),
+            _ci(p.rsplit * p.qsplit), _ci(p.qsplit), _cd(grid.rearth), _cd(1.0 / grid.rearth), _ci(1),
             _ci(p.pgrad_correction), _cd(p.dp3d_thresh), _cd(p.vtheta_thresh), _ci(0), _ci(0),
             _cd(p.tom_sponge_start))
         L.init_hvcoord_c(_cd(hv.ps0), _pp(hv.hyam), _pp(hv.hyai), _pp(hv.hybm), _pp(hv.hybi))

@@ -4,7 +4,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libthetal_b200.so")
+# THETAL_B200_LIB: alternative build of the same library (kernel tuning variants, tools/bench_dirk.py)
+LIB_PATH = os.environ.get("THETAL_B200_LIB") or os.path.join(_HERE, "csrc", "libthetal_b200.so")
 _lib = None
 
 # every symbol include/thetal_b200.h declares
@@ -24,6 +25,7 @@ SYMBOLS = [
     "thetal_b200_time_steps", "thetal_b200_launch_count", "thetal_b200_profile_step",
     "thetal_b200_push_level", "thetal_b200_pull_level", "thetal_b200_pin_host", "thetal_b200_enqueue_step",
     "thetal_b200_halo_counts", "thetal_b200_halo_lists", "thetal_b200_dss_table", "thetal_b200_halo_stats", "thetal_b200_global_diagnostics", "vertical_remap_c", "thetal_b200_pipeline_step", "thetal_b200_pipeline_flush", "thetal_b200_set_vertical_remap",
+    "thetal_b200_time_dirk",
 ]
 
 
@@ -37,5 +39,6 @@ def load():
         _lib.thetal_b200_last_error.restype = ctypes.c_int
         _lib.thetal_b200_last_error_msg.restype = ctypes.c_char_p
         _lib.thetal_b200_time_steps.restype = ctypes.c_double
+        _lib.thetal_b200_time_dirk.restype = ctypes.c_double
         _lib.thetal_b200_launch_count.restype = ctypes.c_long
     return _lib
