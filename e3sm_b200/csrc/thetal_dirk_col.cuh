@@ -71,7 +71,7 @@ __device__ __forceinline__ double div_p0(double x)
 __device__ __forceinline__ double gwphis_of(double dk, double dm, double v1k, double v1m, double v2k, double v2m,
                                             double g1, double g2, double hyb)
 {
-  const double r = rcp46(dk + dm);
+  const double r = rcp_fast(dk + dm);
   const double n1 = dk * v1k + dm * v1m, n2 = dk * v2k + dm * v2m;
   double q1 = n1 * r, q2 = n2 * r;
   q1 = fma(fma(-q1, dk + dm, n1), r, q1);
@@ -82,7 +82,7 @@ __device__ __forceinline__ double gwphis_of(double dk, double dm, double v1k, do
 // EOS of one level from dphi (EOS:175-183): pnh and c = pnh/dphi (IM:417) with one reciprocal
 __device__ __forceinline__ void eos_level(double rth, double dphi, double &pnh, double &c)
 {
-  const double r = rcp46(dphi);                       // 1/dphi (< 0)
+  const double r = rcp_fast(dphi);                       // 1/dphi (< 0)
   const double q0 = -(rth * r);
   const double poe = fma(fma(q0, dphi, rth), -r, q0); // Rgas*vtheta_dp/(-dphi), <= 1 ulp
   pnh = P0 * thetal_pow::pow_pos(div_p0(poe), C_GAMMA);
@@ -194,7 +194,9 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     dp[i] = cdp[kk]; phi0[i] = cphi[kk]; v1[i] = cv1[kk]; v2[i] = cv2[kk];
     if (valid && (th < 0 || dp[i] < 0)) bad = 1;
     const double dpi = (k > 0) ? (dp[i] + (i > 0 ? dp[i > 0 ? i - 1 : 0] : dpm0)) / 2 : dp[i];
-    rdpi[i] = div_fast(1.0, dpi);
+    // padded rows (k >= nlev) get constants that make them identity rows with a zero right-hand side
+    // without any select inside the Newton loop: 1/dp_i = 0, w = 0, w0 = dt2*g, dphi0 = dphi = -g
+    rdpi[i] = valid ? div_fast(1.0, dpi) : 0.0;
     rth[i] = RGAS * th;
     w0[i] = valid ? cw[kk] : 0.0;
     wmax = fmax(wmax, fabs(w0[i]));
@@ -289,9 +291,9 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       const double phb = lastlev ? phis : (inlane ? ph[inlane ? i + 1 : i] : ph_next);
       const double p0b = lastlev ? phis : (inlane ? phi0[inlane ? i + 1 : i] : p0_next);
       double d = phb - ph[i];
-      s_dphi0[i * NT] = p0b - phi0[i];
+      s_dphi0[i * NT] = (k < nlev) ? p0b - phi0[i] : -g;
       if (k < nlev && d > -g) { d = -g; nsafe = 1; }
-      dphi[i] = (k < nlev) ? d : -g;                          // padded rows: any harmless negative value
+      dphi[i] = (k < nlev) ? d : -g;
     }
     if (nsafe) sflag = 1;
     __syncthreads();
@@ -306,7 +308,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
       w[i] = (k0 + i < nlev) ? div_fast(ph[i] - phi0[i], dtg) : 0.0;
-      s_w0[i * NT] = w0[i];
+      s_w0[i * NT] = (k0 + i < nlev) ? w0[i] : dtg;
       s_phi0[i * NT] = phi0[i];
     }
   }
@@ -330,17 +332,18 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       double cm = __shfl_up_sync(FULLMASK, cc[ITEMS - 1], 1, TPC);
 #pragma unroll
       for (int i = 0; i < ITEMS; i++) {
-        const int k = k0 + i;
-        const bool first = (k == 0), last = (k == nlev - 1), valid = (k < nlev);
+        const bool first = (i == 0) && (j == 0);                  // level 1: IM:419-422, EOS:198
         const double bk = ajac * rdpi[i];
         const double mu = ((first ? 2.0 : 1.0) * (pnh[i] - (first ? ptop : pm))) * rdpi[i];
         const double Fn = w[i] - (s_w0[i * NT] + dtg * (mu - 1));
         const double lo = first ? 0.0 : bk * cm;
         const double up = (first ? 2.0 : 1.0) * (bk * cc[i]);
-        sub[i] = valid ? lo : 0.0;
-        dg[i] = valid ? (1 - lo - up) : 1.0;
-        sup[i] = (valid && !last) ? up : 0.0;
-        rhs[i] = valid ? -Fn : 0.0;
+        sub[i] = lo;
+        dg[i] = 1 - lo - up;
+        // the super-diagonal of level nlev (IM:430-432 has none) multiplies the unknown of the padded row
+        // behind it, which is exactly zero; only a column that fills every row needs the explicit zero
+        sup[i] = (i == ITEMS - 1 && j == TPC - 1) ? 0.0 : up;
+        rhs[i] = -Fn;
         pm = pnh[i]; cm = cc[i];
       }
     }
@@ -349,7 +352,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     f[0] = sub[0];
 #pragma unroll
     for (int i = 1; i < M; i++) {
-      rinv[i - 1] = rcp46(dg[i - 1]);
+      rinv[i - 1] = rcp_fast(dg[i - 1]);
       const double l = sub[i] * rinv[i - 1];
       dg[i] = fma(-l, sup[i - 1], dg[i]);
       rhs[i] = fma(-l, rhs[i - 1], rhs[i]);
@@ -373,7 +376,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       const double Rd = __shfl_down_sync(FULLMASK, R0, 1, TPC);
       const double cl = sup[M - 1];                   // zero in the last lane (last level or padding)
       const double D = fma(-cl, Fd, dg[M - 1]);
-      const double rD = rcp46(D);
+      const double rD = rcp_fast(D);
       Ar = f[M - 1] * rD;
       Cr = -(cl * Gd) * rD;
       Rr = fma(-cl, Rd, rhs[M - 1]) * rD;
@@ -381,16 +384,16 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     //    parallel cyclic reduction over the TPC lanes of the column, rows normalised to unit diagonal
 #pragma unroll
     for (int s = 1; s < TPC; s <<= 1) {
-      double Au = __shfl_up_sync(FULLMASK, Ar, s, TPC), Cu = __shfl_up_sync(FULLMASK, Cr, s, TPC);
-      double Ru = __shfl_up_sync(FULLMASK, Rr, s, TPC);
-      double Ad = __shfl_down_sync(FULLMASK, Ar, s, TPC), Cd = __shfl_down_sync(FULLMASK, Cr, s, TPC);
-      double Rd = __shfl_down_sync(FULLMASK, Rr, s, TPC);
-      if (j < s) { Au = 0.0; Cu = 0.0; Ru = 0.0; }
-      if (j + s >= TPC) { Ad = 0.0; Cd = 0.0; Rd = 0.0; }
+      // lanes j < s have Ar = 0 and lanes j >= TPC - s have Cr = 0 at this point (induction from A = 0 in
+      // lane 0 and C = 0 in the last lane), so the values a shuffle returns for a missing partner (the
+      // lane's own, finite) are multiplied by zero: no range selects
+      const double Cu = __shfl_up_sync(FULLMASK, Cr, s, TPC), Ru = __shfl_up_sync(FULLMASK, Rr, s, TPC);
+      const double Ad = __shfl_down_sync(FULLMASK, Ar, s, TPC), Rd = __shfl_down_sync(FULLMASK, Rr, s, TPC);
       const double Dn = fma(-Cr, Ad, fma(-Ar, Cu, 1.0));
-      const double rD = rcp46(Dn);
+      const double rD = rcp_fast(Dn);
       Rr = fma(-Cr, Rd, fma(-Ar, Ru, Rr)) * rD;
-      if (2 * s < TPC) {
+      if (2 * s < TPC) {            // the last round only needs the right-hand side
+        const double Au = __shfl_up_sync(FULLMASK, Ar, s, TPC), Cd = __shfl_down_sync(FULLMASK, Cr, s, TPC);
         const double An = -(Ar * Au) * rD, Cn = -(Cr * Cd) * rD;
         Ar = An; Cr = Cn;
       }
@@ -399,25 +402,25 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     double x[ITEMS];
     x[M - 1] = Rr;
     {
-      double sp = __shfl_up_sync(FULLMASK, Rr, 1, TPC);
-      if (j == 0) sp = 0.0;
+      const double sp = __shfl_up_sync(FULLMASK, Rr, 1, TPC);      // lane 0: f = 0
 #pragma unroll
       for (int i = 0; i < M - 1; i++) x[i] = fma(-gq[i], Rr, fma(-f[i], sp, rhs[i])) * rinv[i];
     }
     // dphi update (IM:278-283), positivity check, w update (IM:320-322)
-    const double x_next = __shfl_down_sync(FULLMASK, x[0], 1, TPC);
-    const double w_next = __shfl_down_sync(FULLMASK, w[0], 1, TPC);
+    // level nlev uses  dphi0 - dt2 g (w + x)  (IM:282): the same expression with w = x = 0 below it, which is
+    // what the padded row behind it holds; the one slot with no row behind it gets explicit zeros
+    double x_next = __shfl_down_sync(FULLMASK, x[0], 1, TPC);
+    double w_next = __shfl_down_sync(FULLMASK, w[0], 1, TPC);
+    if (j == TPC - 1) { x_next = 0.0; w_next = 0.0; }
     int anypos = 0;
     double xmax = 0.0;
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
-      const int k = k0 + i;
       const bool inlane = (i + 1 < ITEMS);
       const double xb = inlane ? x[inlane ? i + 1 : i] : x_next, wb = inlane ? w[inlane ? i + 1 : i] : w_next;
-      double d;
-      if (k < nlev - 1) d = s_dphi0[i * NT] + dtg * ((wb - w[i]) + (xb - x[i]));
-      else d = s_dphi0[i * NT] - dtg * (w[i] + x[i]);
-      if (k < nlev) { dphi[i] = d; if (d >= 0) anypos = 1; }
+      const double d = s_dphi0[i * NT] + dtg * ((wb - w[i]) + (xb - x[i]));
+      dphi[i] = d;
+      if (d >= 0) anypos = 1;
       xmax = fmax(xmax, fabs(x[i]));
     }
     double alpha = 1.0;
@@ -431,9 +434,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
         const int k = k0 + i;
         const bool inlane = (i + 1 < ITEMS);
         const double xb = inlane ? x[inlane ? i + 1 : i] : x_next, wb = inlane ? w[inlane ? i + 1 : i] : w_next;
-        double dx, dw;
-        if (k < nlev - 1) { dx = xb - x[i]; dw = wb - w[i]; }
-        else { dx = -x[i]; dw = -w[i]; }
+        const double dx = xb - x[i], dw = wb - w[i];
         if (k < nlev && dx != 0) {
           const double alpha_k = -(s_dphi0[i * NT] + dtg * dw) / (dtg * dx);
           if (alpha_k >= 0) amin = fmin(amin, alpha_k);
@@ -447,10 +448,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
           const int k = k0 + i;
           const bool inlane = (i + 1 < ITEMS);
           const double xb = inlane ? x[inlane ? i + 1 : i] : x_next, wb = inlane ? w[inlane ? i + 1 : i] : w_next;
-          double d;
-          if (k < nlev - 1) d = s_dphi0[i * NT] + dtg * ((wb - w[i]) + alpha * (xb - x[i]));
-          else d = s_dphi0[i * NT] - dtg * (w[i] + alpha * x[i]);
-          if (k < nlev) dphi[i] = d;
+          if (k < nlev) dphi[i] = s_dphi0[i * NT] + dtg * ((wb - w[i]) + alpha * (xb - x[i]));
         }
       }
     }

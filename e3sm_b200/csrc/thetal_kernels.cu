@@ -145,7 +145,7 @@ __device__ constexpr thetal_pow::PowConst C_GAMMA = {1.0 / (1.0 - KAPPA), 0.0, 2
 __device__ constexpr thetal_pow::PowConst C_KM1 = {KAPPA - 1.0, 0.0, -1.0306441110016318, -8.6951363107339526e-17};
 static_assert(1.0 / (1.0 - KAPPA) == 1.3997994317232159 && KAPPA - 1.0 == -0.71438805970149244, "pow constants");
 using thetal_pow::div_fast;
-using thetal_pow::rcp46;
+using thetal_pow::rcp_fast;
 
 __device__ __forceinline__ double eos_pnh(double p_over_exner)
 {
@@ -734,7 +734,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
     const double dphi = spnh[qq];
     if (q < n16 && dphi > 0) bad = 1;   // (a clamped duplicate may read a slot already overwritten)
     const double pnh = eos_pnh(div_fast(rth[j], -dphi));                            // IM:261
-    const double cq = pnh * rcp46(dphi);
+    const double cq = pnh * rcp_fast(dphi);
     if (q < n16) {
       sw[q] = w_guess;
       spnh[q] = pnh;
@@ -781,7 +781,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
           double *wc = sc + p, *wx = sx + p;
           double cprev = pc[0];
           double Uprev = 2 * (ajac * pd[0]) * cprev;
-          double r = rcp46(1 - Uprev);
+          double r = rcp_fast(1 - Uprev);
           double y = wx[0];
           myc = Uprev * r; myy = y * r;
           wc[0] = myc; wx[0] = myy;
@@ -794,7 +794,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
             const double diag = 1 - L - U;
             const double P = fma(-(L * Uprev), r, diag);
             y = fma(-(L * r), y, rhs);
-            r = rcp46(P);
+            r = rcp_fast(P);
             myc = U * r; myy = y * r;
             wc[0] = myc; wx[0] = myy;
             Uprev = U; cprev = c;
@@ -808,7 +808,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
           double cm1 = (nlev - 2 >= m) ? pc[-16] : c_edge;
           const double b0 = ajac * pd[0];
           double Lprev = b0 * cm1;
-          double r = rcp46(1 - Lprev - b0 * c);
+          double r = rcp_fast(1 - Lprev - b0 * c);
           double y = wx[0];
           myc = Lprev * r; myy = y * r;
           wc[0] = myc; wx[0] = myy;
@@ -823,7 +823,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
             const double diag = 1 - L - U;
             const double P = fma(-(U * Lprev), r, diag);
             y = fma(-(U * r), y, rhs);
-            r = rcp46(P);
+            r = rcp_fast(P);
             myc = L * r; myy = y * r;
             wc[0] = myc; wx[0] = myy;
             Lprev = L;
@@ -835,7 +835,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
       asm volatile("bar.sync 1, 64;" ::: "memory");
       if ((tid & 31) < 16) {
         const double cp = red[80 + p], yp = red[96 + p], lp = red[112 + p], zp = red[128 + p];
-        const double xm = (zp - lp * yp) * rcp46(1 - lp * cp);
+        const double xm = (zp - lp * yp) * rcp_fast(1 - lp * cp);
         if (!up) {
           double x = yp - cp * xm;
           double *wx = sx + (m - 1) * 16 + p;
@@ -941,7 +941,7 @@ __global__ void __launch_bounds__(DIRK_THREADS, (ITEMS >= 6 ? 2 : DIRK_MINB)) di
       const double dphi = sr[qq];
       if (q < n16 && dphi > 0) bad = 1;
       const double pnh = eos_pnh(div_fast(rth[j], -dphi));                          // IM:324
-      const double cq = pnh * rcp46(dphi);
+      const double cq = pnh * rcp_fast(dphi);
       if (q < n16) {
         spnh[q] = pnh;
         sc[q] = cq;
