@@ -43,13 +43,13 @@ class ClockSampler:
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, dev):
-        self.dev, self.rows, self.proc = dev, [], None
+    def __init__(self, dev, period_ms=100):
+        self.dev, self.rows, self.proc, self.period = dev, [], None, int(period_ms)
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.dev}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", str(self.period)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -111,20 +111,30 @@ def barrier(td):
 
 
 # ------------------------------------------------------------------------------------------------
+def fortran_toolchain_note():
+    """probe for the reference's own toolchain at run time."""
+    import shutil
+    found = [t for t in ("mpif90", "gfortran", "ifort", "ifx", "nvfortran", "ftn") if shutil.which(t)]
+    if found:
+        return ("Fortran compiler present (" + ", ".join(found) + ") but the reference build also needs MPI, NetCDF/PIO and "
+                "cmake-generated sources: not built; CPU restatement of the Fortran routines timed instead")
+    return ("reference Fortran+MPI build unavailable on this box (probed mpif90, gfortran, ifort, ifx, nvfortran, ftn: "
+            "none found); CPU restatement of the Fortran routines (oracle/, kind 'port') timed instead")
+
+
 def cpu_reference_sample(p, seconds_target=12.0, warmup=1, steps=None):
-    """Time the oracle (reference algorithm restated, -O3, OpenMP over elements) on all host cores
-    on a bounded sample of the workload: the same configuration (nlev, stepper, hyperviscosity) on a
-    coarser ne8 sphere (384 elements), since the oracle needs a closed sphere for its DSS."""
+    """Time the oracle (reference algorithm restated in C, -O3, OpenMP over elements) on all host cores on
+    the ACTUAL configuration p (same sphere, levels, stepper, hyperviscosity); the sample is bounded in the
+    number of dynamics steps, not in the size of the problem."""
     from e3sm_b200.dycore import build_case
     from oracle.oracle import Oracle
     cores = os.cpu_count() or 1
-    ps = p.with_(ne=8)
-    grid, hv, st, phis, gradphis, refs = build_case(ps)
-    o = Oracle(grid, hv, ps, phis, gradphis, refs, st, nthreads=cores, fast=True)
+    grid, hv, st, phis, gradphis, refs = build_case(p)
+    o = Oracle(grid, hv, p, phis, gradphis, refs, st, nthreads=cores, fast=True)
     tl = [0, 1, 2]
 
     def one():
-        o.prim_advance_exp(ps.tstep, tl[0], tl[1], tl[2])
+        o.prim_advance_exp(p.tstep, tl[0], tl[1], tl[2])
         tl[0], tl[1], tl[2] = tl[1], tl[2], tl[0]
 
     for _ in range(warmup):
@@ -132,32 +142,41 @@ def cpu_reference_sample(p, seconds_target=12.0, warmup=1, steps=None):
     t0 = time.perf_counter()
     one()
     t1 = time.perf_counter() - t0
-    n = steps if steps is not None else max(1, min(200, int(seconds_target / max(t1, 1e-3))))
+    n = steps if steps is not None else max(2, min(200, int(seconds_target / max(t1, 1e-3))))
     t0 = time.perf_counter()
     for _ in range(n):
         one()
     el = time.perf_counter() - t0
     assert o.error_flag == 0
     val = grid.nelem * n / el
-    sample = (f"ne8np4 L{ps.nlev} sphere (384 elements), {n} steps of the C2 step "
-              f"(tstep_type {ps.tstep_type}, hvs {ps.hypervis_subcycle}), {el:.1f} s, oracle -O3 OpenMP")
+    sample = (f"ne{p.ne}np4 L{p.nlev} sphere ({grid.nelem} elements, the configuration itself), {n} dynamics steps "
+              f"(tstep_type {p.tstep_type}, hvs {p.hypervis_subcycle}), {el:.1f} s, oracle -O3 OpenMP over elements")
     return val, cores, sample, el / n
+
+
+def workload_string(name, p, nelem_total, weak_ne=0):
+    dev = ""
+    if name == "C2":
+        dev = (", nu_div = nu = 1e15 (deviates from the SURVEY/BASELINE C2 value nu_div = 2.5e15, which is unstable at "
+               "one hyperviscosity subcycle in the oracle and on the GPU alike: DESIGN.md section 6)")
+    return (f"{name}{' (weak scaling: ne = 30*sqrt(N), ~5400 elements per GPU)' if weak_ne else ''}"
+            f": theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem_total} elements"
+            f", tstep_type {p.tstep_type}, dt={p.tstep:g}s, hypervis_subcycle {p.hypervis_subcycle}, "
+            f"nu={p.nu:g}, nu_div={p.nu_div:g}, nu_top={p.nu_top:g}, sponge on{dev}")
 
 
 def run_reference(args, world, rank, td):
     if rank != 0:
         return
     p = config(args.config)
-    # each bench "step" of this arm is a bounded sample: 20 dynamics steps of the 384-element sphere
-    val, cores, sample, sec = cpu_reference_sample(p, warmup=max(1, min(args.warmup, 2)), steps=20 * args.steps)
+    K = args.steps
+    val, cores, sample, sec = cpu_reference_sample(p, warmup=max(1, min(args.warmup, 2)), steps=K)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3 * p.nelem / 384.0,
+        "steps": K, "warmup": args.warmup, "ms_per_step": sec * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": f"{args.config}: theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, dt={p.tstep:g}s",
-                   "note": "reference Fortran+MPI build unavailable on this box (no Fortran compiler); "
-                           "CPU restatement of the Fortran routines timed instead; ms_per_step scaled to 5400 elements"},
+        "config": {"workload": workload_string(args.config, p, p.nelem), "note": fortran_toolchain_note()},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "sypd": p.tstep * (val / p.nelem) / 365.0,
@@ -165,14 +184,22 @@ def run_reference(args, world, rank, td):
     print(json.dumps(line), flush=True)
 
 
-def run_ours(args, world, rank, local, td):
-    import ctypes
-    from e3sm_b200.dycore import ThetaLDycore, broadcast_nccl_id, build_case, _ci, _cd
-    from e3sm_b200.initial import State
+def gather_bits(td, vec):
+    """all ranks' copies of a small float64 vector, as raw bit patterns (rank-major)."""
+    a = np.ascontiguousarray(vec, dtype=np.float64).view(np.int64)
+    if td is None:
+        return a[None, :]
+    import torch
+    dev = "cuda" if td.get_backend() == "nccl" else "cpu"
+    t = torch.from_numpy(a.copy()).to(dev)
+    out = [torch.empty_like(t) for _ in range(td.get_world_size())]
+    td.all_gather(out, t)
+    return np.stack([o.cpu().numpy() for o in out])
+
+
+def make_dycore(p, world, rank, local, td):
+    from e3sm_b200.dycore import ThetaLDycore, broadcast_nccl_id, build_case
     from e3sm_b200.partition import Partition
-    p = config(args.config)
-    if args.weak_ne:
-        p = weak_scaled(p, args.weak_ne)      # dt ~ 1/ne, nu ~ (30/ne)^3.2, nu_top ~ 1/ne
     part, nccl_id = None, None
     if world > 1:   # elements cut along HOMME's space-filling curve, one slice per GPU, DSS halos over NCCL
         part = Partition(p.ne, world)
@@ -180,22 +207,86 @@ def run_ours(args, world, rank, local, td):
     grid, hv, st, phis, gradphis, refs = build_case(p, part=part, rank=rank)
     d = ThetaLDycore(grid, hv, p, phis, gradphis, refs, device=local, rank=rank, part=part, nccl_id=nccl_id)
     d.set_state(st)
+    return d, grid, hv
+
+
+def timed_steps(d, p, td, W, K, tl=(0, 1, 2)):
+    """W untimed + K timed dynamics steps with the state resident; device time (CUDA events on the library
+    stream), barrier on both sides, max over ranks.  Also checks the answer: dry mass (global mean surface
+    pressure, reproducible sum on the device) must not drift, and every rank must hold the same bits."""
+    nm1, n0, np1 = tl
+    diag0 = d.global_diagnostics(n0)
+    _, nm1, n0, np1 = d.time_steps(p.tstep, W, nm1, n0, np1)
+    barrier(td)
+    ms, nm1, n0, np1 = d.time_steps(p.tstep, K, nm1, n0, np1)
+    barrier(td)
+    ms = all_max(td, ms)
+    diag1 = d.global_diagnostics(n0)
+    drift = abs(diag1["ps_mean"] - diag0["ps_mean"]) / diag0["ps_mean"]
+    keys = ("ps_min", "ps_max", "ps_mean", "KE", "PE", "IE", "energy")
+    bits = gather_bits(td, [diag1[k] for k in keys])
+    same = bool((bits == bits[0]).all())
+    check = {"dry_mass_rel_drift": drift, "steps": W + K, "ranks_bitwise_identical": same,
+             "ps_min": diag1["ps_min"], "energy": diag1["energy"]}
+    assert drift <= 1e-11, f"dry mass drifted by {drift:.3e} over {W + K} steps"
+    assert same, "global diagnostics differ between ranks"
+    assert np.isfinite(diag1["energy"])
+    return ms, (nm1, n0, np1), check
+
+
+def strong_scaling_block(world, rank, local, td, K=5, W=2):
+    """BASELINE.json config 3 (ne120np4 L72, hypervis_subcycle 4) on the N GPUs of this run and, on rank 0
+    alone, on one GPU: the north-star strong-scaling pair, timed inside the driver-run line."""
+    p3 = config("C3")
+    d, grid, hv = make_dycore(p3, world, rank, local, td)
+    nelem_total = grid.nelem
+    ms_n, _, chk = timed_steps(d, p3, td, W, K)
+    n_exch, halo_bytes = d.halo_stats()
+    d.close()
+    ms_1 = 0.0
+    if rank == 0:
+        d1, _, _ = make_dycore(p3, 1, 0, local, None)
+        ms_1, _, _ = timed_steps(d1, p3, None, W, K)
+        d1.close()
+    ms_1 = all_max(td, ms_1)
+    barrier(td)
+    return {"config": workload_string("C3", p3, nelem_total), "scaling": "strong", "steps": K, "warmup": W,
+            "n1_ms_per_step": ms_1 / K, "nN_ms_per_step": ms_n / K, "n_gpus": world,
+            "efficiency": (ms_1 / K) / (world * ms_n / K),
+            "value_nN": nelem_total * K / (ms_n * 1e-3), "value_n1": nelem_total * K / (ms_1 * 1e-3),
+            "halo_MB_per_exchange_rank0": halo_bytes / max(n_exch, 1) / 1e6, "answer_check": chk}
+
+
+def run_ours(args, world, rank, local, td):
+    import ctypes
+    from e3sm_b200.dycore import _ci, _cd
+    from e3sm_b200.initial import State
+    p = config(args.config)
+    if args.weak_ne:
+        p = weak_scaled(p, args.weak_ne)      # dt ~ 1/ne, nu ~ (30/ne)^3.2, nu_top ~ 1/ne
+    d, grid, hv = make_dycore(p, world, rank, local, td)
     L = d.L
     nelem, nlev = d.nelem, hv.nlev          # elements on this GPU
     nelem_total = grid.nelem
     K, W = args.steps, max(args.warmup, 3)
-    # ---- device-resident timing ----
-    ms_w, nm1, n0, np1 = d.time_steps(p.tstep, W, 0, 1, 2)
+    # ---- device-resident timing: W warm-up + exactly K timed steps ----
     l0 = d.launch_count()
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, period_ms=20)
     sampler.start()
-    barrier(td)
-    ms, nm1, n0, np1 = d.time_steps(p.tstep, K, nm1, n0, np1)
-    barrier(td)
+    ms, (nm1, n0, np1), answer = timed_steps(d, p, td, W, K)
     clocks = sampler.stop()
-    launches = d.launch_count() - l0
-    ms = all_max(td, ms)
+    launches_per_step = (d.launch_count() - l0 - 4) // (W + K)     # 2 x 2 diagnostics launches
+    launches = launches_per_step * K
     value = nelem_total * K / (ms * 1e-3)
+    # ---- the same step sustained for >= 1.5 s so the in-line clock record has enough samples ----
+    n_sus = max(K, int(1500.0 / max(ms / K, 1e-3)))
+    sampler = ClockSampler(local, period_ms=100)
+    sampler.start()
+    ms_sus, nm1, n0, np1 = d.time_steps(p.tstep, n_sus, nm1, n0, np1)
+    clocks_sus = sampler.stop()
+    ms_sus = all_max(td, ms_sus)
+    clocks["sustained"] = {"steps": n_sus, "ms_per_step": ms_sus / n_sus, "sm_mhz": clocks_sus["sm_mhz"],
+                           "reasons": clocks_sus["reasons"], "samples": clocks_sus.get("samples", 0)}
     # ---- per-kernel-family times of one step (CUDA events on the library stream) ----
     fam = (ctypes.c_double * 8)()
     reps = 3
@@ -215,23 +306,59 @@ def run_ours(args, world, rank, local, td):
     # algorithmic bytes per launch of each family, tstep_type 9: 5 launches each
     alg = {"caar_pre": (14 * S + 4 * Dv) / 5.0, "caar_dss_post": 2 * S, "dirk": (7 * S + 10 * I) / 5.0}
     nl = {"caar_pre": 5, "caar_dss_post": 5, "dirk": 5}
+    kname = {"caar_pre": "caar_pre_kernel", "caar_dss_post": "caar_dss_post_kernel", "dirk": "dirk_col_kernel"}
     dom = max(nl, key=lambda k: fam_ms[k])
     dom_ms = fam_ms[dom] / nl[dom]
     ach = nelem * alg[dom] / (dom_ms * 1e-3) / 1e9
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
     if os.path.exists(tpath) and world == 1:
         tj = json.load(open(tpath))
-        if tj.get("workload") == args.config and (dom + "_kernel") in tj:
-            traffic = tj[dom + "_kernel"]["traffic_bytes_per_launch"]
-    roofline = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+        if tj.get("workload") == args.config and kname[dom] in tj:
+            traffic = tj[kname[dom]]["traffic_bytes_per_launch"]
+    fp64_peak = float(L.thetal_b200_measure_fp64_peak())
+    roofline = {"bound": "hbm", "kernel": kname[dom], "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": traffic, "peak_kind": peak_kind,
-                "alg_bytes_per_launch": nelem * alg[dom], "launch_ms": dom_ms}
+                "alg_bytes_per_launch": nelem * alg[dom], "launch_ms": dom_ms,
+                "note": "average over the family's 5 launches per step (the last DIRK stage also reads state(n0), state(nm1)); "
+                        "the kernel is FP64/XU-pipe bound, not HBM bound: see fp64 and profiles/r2_ncu_summary.txt",
+                "by_family": {k: {"launch_ms": fam_ms[k] / nl[k], "GBps": nelem * alg[k] / (fam_ms[k] / nl[k] * 1e-3) / 1e9,
+                                  "frac": nelem * alg[k] / (fam_ms[k] / nl[k] * 1e-3) / 1e9 / peak} for k in nl}}
     step_gbs = nelem_total * bstep / (ms / K * 1e-3) / 1e9
-    # ---- end to end through the C ABI with host buffers ----
+    # ---- end to end through the reference's own call triple, Fortran-layout host arrays ----
+    # init_elements_states_c (H2D, all three time levels) -> prim_run_subcycle_c (rsplit*qsplit dynamics
+    # steps + vertical remap, what the Fortran driver calls per model step) -> cxx_push_results_to_f90 (D2H)
     hst = State(nelem, nlev)
     d.get_state(hst)
+    for f in State.FIELDS:
+        a = getattr(hst, f)
+        L.thetal_b200_pin_host(ctypes.c_void_p(a.ctypes.data), ctypes.byref(ctypes.c_long(a.nbytes)), _ci(1))
+    d.init_time_level(nm1 + 1, n0 + 1, np1 + 1)
+    steps_per_call = p.rsplit * p.qsplit
+
+    def triple():
+        d.set_state(hst)
+        d.prim_run_subcycle(p.tstep)
+        d.get_state(hst)
+
+    triple()
+    Kt = max(2, min(6, K))
+    barrier(td)
+    t0 = time.perf_counter()
+    for _ in range(Kt):
+        triple()
+    e2e_t = all_max(td, time.perf_counter() - t0)
+    d._check()
+    e2e_val = nelem_total * Kt * steps_per_call / e2e_t
+    state_bytes = nelem_total * 3 * S
+    assert all(np.isfinite(getattr(hst, f)).all() for f in State.FIELDS)
+    for f in State.FIELDS:
+        a = getattr(hst, f)
+        L.thetal_b200_pin_host(ctypes.c_void_p(a.ctypes.data), ctypes.byref(ctypes.c_long(a.nbytes)), _ci(0))
+    # ---- single-level variants (builder-added entry points), kept as labelled extras ----
+    nm1, n0, np1 = 0, 1, 2
     lev = {f: [np.ascontiguousarray(getattr(hst, f)[:, t]) for t in range(3)] for f in State.FIELDS}
+    del hst
     for f in State.FIELDS:
         for t in range(3):
             a = lev[f][t]
@@ -245,6 +372,8 @@ def run_ours(args, world, rank, local, td):
         L.thetal_b200_enqueue_step(_cd(p.tstep), _ci(a), _ci(b), _ci(c))
         L.thetal_b200_pull_level(_ci(c), ptr("v", c), ptr("w_i", c), ptr("vtheta_dp", c), ptr("phinh_i", c), ptr("dp3d", c))
 
+    for t in range(3):      # the pulled host levels are consistent with the device again
+        L.thetal_b200_push_level(_ci(t), ptr("v", t), ptr("w_i", t), ptr("vtheta_dp", t), ptr("phinh_i", t), ptr("dp3d", t))
     Ke = max(3, min(K, 10))
     for _ in range(2):
         e2e_step(nm1, n0, np1)
@@ -284,15 +413,19 @@ def run_ours(args, world, rank, local, td):
     L.thetal_b200_pipeline_flush()
     e2e_p = all_max(td, time.perf_counter() - t0)
     d._check()
-    e2e_val = nelem_total * Kp / e2e_p
+    e2e_batch = nelem_total * Kp / e2e_p
     for f in State.FIELDS:                      # both output buffers hold the step of the same input
         assert np.array_equal(outs[0][f], outs[1][f]) and np.isfinite(outs[0][f]).all(), f
     level_bytes = nelem_total * S
     n_exch, halo_bytes = d.halo_stats()
+    d.close()
+    strong = None
+    if world > 1 and args.strong:
+        strong = strong_scaling_block(world, rank, local, td)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, cores, sample, _ = cpu_reference_sample(p)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "note": fortran_toolchain_note()}
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -300,9 +433,7 @@ def run_ours(args, world, rank, local, td):
             "scaling": "weak" if (world == 1 or args.weak_ne) else "strong",
             "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.config}{' (weak scaling: ne = 30*sqrt(N), ~5400 elements per GPU)' if args.weak_ne else ''}"
-                                   f": theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem_total} elements"
-                                   f", tstep_type {p.tstep_type}, dt={p.tstep:g}s, hypervis_subcycle {p.hypervis_subcycle}, sponge on",
+            "config": {"workload": workload_string(args.config, p, nelem_total, args.weak_ne),
                        "l2": "inputs larger than L2 (every kernel streams >= 300 MB of state; L2 is 126 MB)",
                        "parallelism": "1 rank per GPU" + ("" if world == 1 else
                                       f", HOMME space-filling-curve partition into {world} slices ({nelem} elements on rank 0), "
@@ -312,18 +443,28 @@ def run_ours(args, world, rank, local, td):
             "hbm_gbs_step": step_gbs, "hbm_frac_step": step_gbs / (peak * world), "alg_bytes_per_element_step": bstep,
             "kernel_ms_per_step": fam_ms,
             "roofline": roofline,
-            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": level_bytes, "d2h_bytes_per_step": level_bytes,
-                    "steps": Kp, "serial_value": e2e_serial, "serial_steps": Ke,
-                    "note": "thetal_b200_pipeline_step: per step pinned-host state(n0) -> device, prim_advance_exp, "
-                            "state(np1) -> pinned host; independent batches, the three phases of consecutive steps "
-                            "overlap on three streams (timed with the pipeline fill and drain). serial_value: the same "
-                            "three phases back to back on one stream"},
+            "fp64": {"peak_tflops_measured": fp64_peak,
+                     "how": "independent DFMA chains on every SM (thetal_b200_measure_fp64_peak), CUDA events",
+                     "note": "DIRK and CAAR are bound by the FP64 and XU (MUFU/F2F) pipes; pipe utilisation per kernel "
+                             "from ncu is in profiles/r2_ncu_summary.txt"},
+            "answer_check": answer,
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": state_bytes / steps_per_call,
+                    "d2h_bytes_per_step": state_bytes / steps_per_call, "calls": Kt, "dynamics_steps_per_call": steps_per_call,
+                    "note": "reference call triple per model step, pinned Fortran-layout host arrays (np,np,[2],nlev,timelevels,nelemd): "
+                            "init_elements_states_c (H2D of all three time levels) -> prim_run_subcycle_c (rsplit*qsplit dependent "
+                            "dynamics steps + vertical remap) -> cxx_push_results_to_f90 (D2H of all three time levels)",
+                    "single_level_serial_value": e2e_serial,
+                    "batch_service_value": e2e_batch,
+                    "batch_service_note": "thetal_b200_pipeline_step (builder-added): INDEPENDENT inputs, one time level in and out "
+                                          f"({level_bytes} B each way), H2D/kernels/D2H of consecutive calls overlapped; not attainable "
+                                          "by a time-stepping caller, whose step j+1 consumes step j"},
             "gpu_launches": launches, "clocks": clocks,
         }
+        if strong:
+            line["strong"] = strong
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
-    d.close()
 
 
 def main():
@@ -335,8 +476,11 @@ def main():
     ap.add_argument("--config", default=None,
                     help="C1..C5; default C2. On N>1 GPUs the default is C2 weak-scaled (ne = round(30*sqrt(N)), "
                          "the same work per element and ~5400 elements per GPU, partitioned along the space-filling "
-                         "curve); pass --config C3 for the ne120 strong-scaling case")
+                         "curve) as `value`, plus a `strong` block: C3 (ne120np4 L72) on the N GPUs and on one GPU; "
+                         "pass --config C3 to make the ne120 strong-scaling case the line's own value")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", dest="strong", action="store_false",
+                    help="skip the C3 strong-scaling block of the default N>1 run")
     args = ap.parse_args()
     world, rank, local, td = dist_setup(args.gpus)
     args.weak_ne = 0
@@ -344,9 +488,11 @@ def main():
         args.config = "C2"
         if world > 1:
             args.weak_ne = int(round(30.0 * world ** 0.5))      # 2: ne42, 4: ne60, 8: ne85
+    else:
+        args.strong = False
     if args.impl == "reference":
         if args.steps > 5:
-            args.steps = 5          # bounded sample: each step is ~1-4 s of CPU work
+            args.steps = 5          # bounded sample: each step is ~0.5 s of CPU work on 16 cores
         run_reference(args, world, rank, td)
     else:
         run_ours(args, world, rank, local, td)

@@ -14,7 +14,9 @@
 #include <cmath>
 #include <map>
 #include <set>
+#include <algorithm>
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>   // header-only; ranges carry the reference's GPTL timer names
 
 using namespace thetal;
 
@@ -574,6 +576,11 @@ struct ProfScope {   // per-family device time when thetal_b200_profile_step is 
   }
 };
 
+struct Nvtx {        // t_startf/t_stopf of the reference (prim_advance_mod.F90:116,591,670,1105,1720; imex_mod.F90:140;
+  explicit Nvtx(const char *name) { nvtxRangePushA(name); }     // viscosity_theta.F90:130), visible to nsys/ncu
+  ~Nvtx() { nvtxRangePop(); }
+};
+
 // ---- bndry_exchangeV (bndry_mod.F90:51-169) for one DSS: pack the partition-boundary points of
 // `t`, ncclSend/ncclRecv with every neighbour rank, unpack into the ghost slots of `t`.
 // nk levels of each field (+ w_i(nlevp) when wbot); all on S.stream, so it is ordered between the
@@ -615,6 +622,7 @@ template <class F> void exchange_and_consume(const StatePtrs &t, int nk, int wbo
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
 void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3)
 {
+  Nvtx r("compute_andor_apply_rhs");
   CaarArgs a;
   a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
   a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
@@ -624,6 +632,7 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
   d.do_limiter = (s3 != 0.0);
   {
     ProfScope ps(1);
+    Nvtx rx("caar_bexchV");
     exchange_and_consume(S.tensA, S.nlev, 1, [&](const int *el, int n) {
       d.elist = el; d.ecount = n; launch_caar_dss_post(d, S.stream); S.launches += 1; });
   }
@@ -632,6 +641,7 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
 
 void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
 {
+  Nvtx r("compute_stage_value_dirk");
   DirkArgs a;
   a.np1 = S.tl[np1]; a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.geo = S.geo; a.prm = S.prm;
   a.dt2 = dt2; a.alphadt_n0 = a_n0; a.alphadt_nm1 = a_nm1;
@@ -643,6 +653,7 @@ void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
 void run_hypervis(int nt, double dt2, double eta_ave_w)
 {
   ProfScope ps(3);
+  Nvtx r("advance_hypervis");
   (void)eta_ave_w;   // dpdiss_ave / dpdiss_biharmonic diagnostics (PA:651-656) are not carried
   HvArgs a;
   a.st = S.tl[nt]; a.geo = S.geo; a.ref = S.ref; a.prm = S.prm;
@@ -655,9 +666,11 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
     a.elist = nullptr; a.ecount = 0;
     a.nu_ratio = nu_ratio1; a.tin = S.tensB; a.tout = S.tensA; launch_hv(0, a, S.stream);
     a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB;
-    exchange_and_consume(S.tensA, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(1, a, S.stream); });
+    { Nvtx rx("biwkdp3d_bexchV");
+      exchange_and_consume(S.tensA, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(1, a, S.stream); }); }
     a.tin = S.tensB; a.tout = S.tensA;
-    exchange_and_consume(S.tensB, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(2, a, S.stream); });
+    { Nvtx rx("ahdp_bexchV2");
+      exchange_and_consume(S.tensB, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(2, a, S.stream); }); }
     a.elist = nullptr; a.ecount = 0;
     S.launches += 3;
   }
@@ -687,6 +700,7 @@ void run_combo(int kind, int ia, int ib, int ic)
 // PA:81-513
 void run_prim_advance_exp(double dt, int nm1, int n0, int np1)
 {
+  Nvtx r("prim_advance_exp");
   const double eta_ave_w = 1.0 / S.prm.qsplit;                                       // PA:137
   launch_wbc(S.tl[n0], S.geo, S.prm.nelem, S.prm.nlev, S.stream);                    // PA:140-143
   S.launches += 1;
@@ -857,6 +871,24 @@ void thetal_b200_sync(void)
   check_device_errors("thetal_b200_sync");
 }
 long thetal_b200_launch_count(void) { return S.launches; }
+
+// Measured FP64 FMA rate of this GPU in TFLOP/s (2 flops per DFMA): independent DFMA chains on every SM,
+// timed with CUDA events on the library stream.  The second roofline axis of the FP64-bound kernels.
+double thetal_b200_measure_fp64_peak(void)
+{
+  REQUIRE_R(S.active, "thetal_b200_measure_fp64_peak before initialize_hommexx_session", -1.0);
+  double best = 0;
+  for (int rep = 0; rep < 4; rep++) {
+    CUDA_OK_R(cudaEventRecord(S.ev0, S.stream), -1.0);
+    const double flops = launch_fp64_peak(S.stream);
+    CUDA_OK_R(cudaEventRecord(S.ev1, S.stream), -1.0);
+    CUDA_OK_R(cudaEventSynchronize(S.ev1), -1.0);
+    float ms = 0;
+    CUDA_OK_R(cudaEventElapsedTime(&ms, S.ev0, S.ev1), -1.0);
+    if (rep > 0 && ms > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+  }
+  return best;
+}
 
 // Partition-boundary tables built by finalize_connectivity (host only, no device needed): used by the
 // CPU tests of the multi-rank host logic and by drivers that want to report halo sizes.

@@ -1378,6 +1378,34 @@ void launch_combo(const ComboArgs &A, cudaStream_t st)
   combo_kernel<<<A.prm.nelem, DSS_THREADS, 0, st>>>(A);
 }
 
+// FP64 FMA peak probe: 8 independent DFMA chains per thread, 1024 threads per CTA, 2 CTAs per SM
+__global__ void __launch_bounds__(1024) fp64_peak_kernel(double *sink, int n)
+{
+  double a[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) a[i] = 1.0 + 1e-3 * (threadIdx.x + i);
+  const double b = 0.99999999, c = 1e-9;
+  for (int it = 0; it < n; it++) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = fma(a[i], b, c);
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) s += a[i];
+  if (s == 123.456) sink[0] = s;
+}
+double launch_fp64_peak(cudaStream_t st)
+{
+  static double *sink = nullptr;
+  if (!sink) cudaMalloc(&sink, sizeof(double));
+  int dev = 0, nsm = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  const int n = 20000, blocks = 2 * nsm;
+  fp64_peak_kernel<<<blocks, 1024, 0, st>>>(sink, n);
+  return 2.0 * 8.0 * (double)n * 1024.0 * blocks;
+}
+
 // PA:140-143  w_i(nlevp,n0) = (v(nlev) . gradphis)/g
 __global__ void wbc_kernel(StatePtrs s, Geo geo, int nelem, int nlev)
 {

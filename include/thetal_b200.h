@@ -180,6 +180,8 @@ void thetal_b200_pipeline_step(const double *dt, const double *v_in, const doubl
 void thetal_b200_pipeline_flush(void);
 void thetal_b200_pin_host(void *ptr, const long *bytes, const int *pin);   /* cudaHostRegister */
 void thetal_b200_enqueue_step(const double *dt, const int *nm1, const int *n0, const int *np1);
+/* measured FP64 FMA rate of this GPU, TFLOP/s (independent DFMA chains on every SM, CUDA events) */
+double thetal_b200_measure_fp64_peak(void);
 /* device ms per launch of compute_stage_value_dirk alone, the same stage problem `reps` times
  * (w_i, phinh_i of np1 restored before every launch); kernel tuning aid (tools/bench_dirk.py) */
 double thetal_b200_time_dirk(const int *nm1, const double *alphadt_nm1, const int *n0, const double *alphadt_n0,
