@@ -26,6 +26,17 @@ if ROOT not in sys.path:
 
 from e3sm_b200.params import bytes_per_element_step, config, weak_scaled  # noqa: E402
 
+# stdout carries exactly ONE JSON line: everything else that writes to fd 1 (NCCL's version banner, library
+# chatter) is sent to stderr, and the line itself goes to the saved descriptor
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 METRIC = "theta-l dycore element-steps/s"
 UNIT = "element-steps/s"
 
@@ -181,7 +192,7 @@ def run_reference(args, world, rank, td):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "sypd": p.tstep * (val / p.nelem) / 365.0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def gather_bits(td, vec):
@@ -464,7 +475,7 @@ def run_ours(args, world, rank, local, td):
             line["strong"] = strong
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 def main():

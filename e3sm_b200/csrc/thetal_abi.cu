@@ -68,6 +68,9 @@ struct Session {
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   cudaEvent_t ev_pin[4]{}, ev_pdone[4]{}, ev_pd2h[4]{};
   long pipe_calls = 0; bool pipe_ready = false;
+  int ftype = -1;           // forcing algorithm (control_mod.F90): 0 and 2 apply the pushed forcing per model step
+  double *d_fm = nullptr, *d_fvtheta = nullptr, *d_fphi = nullptr;   // derived%FM (3 comps), FVTheta, FPHI
+  bool have_forcing = false;
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
   int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
   int overlap = 0;          // measured on 2 and 8 B200: the split launches cost more than the hidden exchange saves
@@ -376,16 +379,18 @@ void init_simulation_params_c(const int *remap_alg, const int *limiter_option, c
   FAIL_IF(*hypervis_scaling != 0.0, 3, "tensor hyperviscosity (hypervis_scaling != 0) is a next-row item (SURVEY 8f N4)");
   FAIL_IF(*laplace_scaling != 0.0, 3, "laplace_scaling != 0 not supported");
   FAIL_IF(*dcmip16_mu != 0.0, 3, "dcmip16_mu != 0 not supported");
-  FAIL_IF(*rsplit <= 0, 3, "rsplit == 0 (vertically Eulerian) not supported by the CUDA path yet");
+  FAIL_IF(*rsplit < 0, 3, "rsplit must be >= 0 (0 = vertically Eulerian, PA:1227-1303)");
   FAIL_IF(*qsplit < 1, 3, "qsplit must be >= 1");
   FAIL_IF(fabs(*laplacian_rigid_factor * *scale_factor - 1.0) > 1e-12, 3,
           "planar geometry (laplacian_rigid_factor != 1/scale_factor) not supported");
   // dt_remap_factor / dt_tracer_factor (prim_driver.cpp:75-88): the dycore-only build has no tracers, so
   // the only consistent setting is dt_tracer_factor = qsplit, dt_remap_factor = rsplit*qsplit (what
   // namelist_mod.F90 derives when the namelist gives rsplit/qsplit); <= 0 means "derive it".
+  // dt_remap_factor = 0 is the vertically Eulerian code (prim_driver.cpp:79-83), i.e. rsplit = 0.
   const int dtf = *dt_tracer_factor > 0 ? *dt_tracer_factor : *qsplit;
   const int drf = *dt_remap_factor > 0 ? *dt_remap_factor : *rsplit * dtf;
   FAIL_IF(drf != *rsplit * dtf, 3, "dt_remap_factor must equal rsplit*dt_tracer_factor (independent remap/tracer steps need tracers: out of scope)");
+  S.ftype = *ftype;
   Params &p = S.prm;
   p.rsplit = *rsplit; p.qsplit = dtf; p.tstep_type = *time_step_type;
   p.theta_advect_form = *theta_adv_form; p.pgrad_correction = *pgrad_correction;
@@ -833,9 +838,35 @@ void init_reference_states_c(thetal_f90ptr theta_ref, thetal_f90ptr dp_ref, thet
   upload_constants(nullptr, nullptr, nullptr, nullptr, S.nu_scale_top.data(), (int)nlev);
 }
 
-void push_forcing_to_c(const double *, const double *, const double *, const double *, const double *)
+// theta_f2c_mod.F90:189-198, cxx_f90_interface_theta.cpp:231-262: derived%FM(np,np,3,nlev,nelemd),
+// FVTheta(np,np,nlev,nelemd), FT (unused by the NH dynamics forcing), FPHI(np,np,nlevp,nelemd); FQ needs
+// tracers (qsize = 0 here).  Applied by prim_run_subcycle_c when ftype is 0 or 2.
+void push_forcing_to_c(const double *fm, const double *fvtheta, const double *ft, const double *fphi, const double *fq)
 {
-  fail(3, "push_forcing_to_c: physics forcing (applyCAMforcing) is outside the hot path of this build");
+  (void)ft; (void)fq;
+  REQUIRE(S.device_ready, "init_functors_c must precede push_forcing_to_c");
+  REQUIRE(fm && fvtheta && fphi, "push_forcing_to_c: FM, FVTheta and FPHI are required");
+  const size_t n = S.prm.nelem, nlev = S.nlev;
+  if (!S.d_fm) {
+    S.d_fm = dalloc<double>(n * 48 * nlev);
+    S.d_fvtheta = dalloc<double>(n * 16 * nlev);
+    S.d_fphi = dalloc<double>(n * 16 * (nlev + 1));
+  }
+  CUDA_OK(cudaMemcpyAsync(S.d_fm, fm, n * 48 * nlev * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaMemcpyAsync(S.d_fvtheta, fvtheta, n * 16 * nlev * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaMemcpyAsync(S.d_fphi, fphi, n * 16 * (nlev + 1) * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  S.have_forcing = true;
+}
+
+// applyCAMforcing_dynamics (PA:517-541, standalone HOMME: FM(3) forces w_i) on time level *nt (0-based)
+void apply_cam_forcing_dynamics_c(const int *nt, const double *dt)
+{
+  REQUIRE(S.device_ready && *nt >= 0 && *nt < NTL, "apply_cam_forcing_dynamics_c: bad state/time level");
+  REQUIRE(S.have_forcing, "apply_cam_forcing_dynamics_c: push_forcing_to_c has not been called");
+  launch_forcing(S.tl[*nt], S.d_fm, S.d_fvtheta, S.d_fphi, S.geo, *dt, S.prm.nelem, S.nlev, S.stream);
+  S.launches += 1;
+  thetal_b200_sync();
 }
 
 void sync_diagnostics_to_host_c(void)
@@ -1071,12 +1102,18 @@ void prim_run_subcycle_c(const double *tstep, int *nstep, int *nm1, int *n0, int
   REQUIRE(S.device_ready, "prim_run_subcycle_c before init");
   REQUIRE(tl_ok(S.nm1) && tl_ok(S.n0) && tl_ok(S.np1) && S.nm1 != S.n0 && S.n0 != S.np1 && S.nm1 != S.np1,
           "prim_run_subcycle_c: init_time_level_c did not set three distinct time levels");
+  // prim_driver.cpp:75-83: dt_remap = dt*dt_remap_factor, or dt*dt_tracer_factor in the Eulerian case
+  const double dt_remap = *tstep * (S.prm.rsplit > 0 ? S.prm.rsplit * S.prm.qsplit : S.prm.qsplit);
+  if ((S.ftype == 0 || S.ftype == 2) && S.have_forcing) {                  // prim_driver.cpp:117-125
+    launch_forcing(S.tl[S.n0], S.d_fm, S.d_fvtheta, S.d_fphi, S.geo, dt_remap, S.prm.nelem, S.nlev, S.stream);
+    S.launches += 1;
+  }
   run_prim_step(*tstep);
   for (int r = 1; r < S.prm.rsplit; r++) {
     leapfrog_update();
     run_prim_step(*tstep);
   }
-  if (S.do_remap) run_vertical_remap(S.np1);
+  if (S.do_remap && S.prm.rsplit > 0) run_vertical_remap(S.np1);          // rsplit = 0: tracers only (none)
   thetal_b200_sync();
   leapfrog_update();
   *nstep = S.nstep; *nm1 = S.nm1; *n0 = S.n0; *np1 = S.np1;

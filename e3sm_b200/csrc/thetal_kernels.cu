@@ -160,16 +160,17 @@ __device__ __forceinline__ double eos_pnh(double p_over_exner)
 constexpr int CAAR_THREADS = 256;
 constexpr int CAAR_SLOTS = 10;    // scratch tiles per half-warp
 
-__host__ __device__ inline size_t caar_smem_bytes(int nlev)
+__host__ __device__ inline size_t caar_smem_bytes(int nlev, bool vadv)
 {
   const size_t nlevp = nlev + 1;
-  // v(2) dp th pnh exn div : 7*nlev tiles ; w phi : 2*nlevp tiles ; scratch
-  return sizeof(double) * 16 * (7 * (size_t)nlev + 2 * nlevp + (CAAR_THREADS / 16) * CAAR_SLOTS);
+  // v(2) dp th pnh exn div : 7*nlev tiles ; w phi : 2*nlevp tiles ; scratch ; rsplit = 0: eta_dot_dpdn at interfaces
+  return sizeof(double) * 16 * (7 * (size_t)nlev + 2 * nlevp + (CAAR_THREADS / 16) * CAAR_SLOTS + (vadv ? nlevp : 0));
 }
 
-// FORM = theta_advect_form, PGRAD = pgrad_correction, ACCUM = (eta_ave_w != 0): compile-time so that the
-// level loop is one straight-line block the scheduler can interleave freely
-template <int FORM, bool PGRAD, bool ACCUM>
+// FORM = theta_advect_form, PGRAD = pgrad_correction, ACCUM = (eta_ave_w != 0), VADV = (rsplit == 0, the
+// vertically Eulerian terms of PA:1227-1303 and prim_si_mod.F90:94-148): compile-time so that the level
+// loop is one straight-line block the scheduler can interleave freely
+template <int FORM, bool PGRAD, bool ACCUM, bool VADV>
 __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArgs A)
 {
   extern __shared__ double smem[];
@@ -184,6 +185,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   double *sexn = spnh + 16 * nlev;
   double *sdiv = sexn + 16 * nlev;
   double *scr = sdiv + 16 * nlev + (tid >> 4) * (CAAR_SLOTS * 16);   // this half-warp's tiles
+  double *seta = sdiv + 16 * nlev + (CAAR_THREADS / 16) * (CAAR_SLOTS * 16);   // [nlevp][16], VADV only
 
   // the nm1 columns are only needed by the final update of each level (PA:1674-1690), and the
   // derived accumulators by their read-modify-write: start them towards L2 now
@@ -234,6 +236,28 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   constexpr int KS = CAAR_THREADS / 16;
   Pt t;
   pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
+  if (VADV) {
+    // eta_dot_dpdn at the interfaces (PA:1227-1251) needs the divergence of every level first
+    for (int k = kslot; k < ((nlev + KS - 1) / KS) * KS; k += KS) {
+      const int kk = k < nlev ? k : nlev - 1, q = kk * 16 + p;
+      double gv1, gv2;
+      div_prep(t, sv[kk * 32 + p] * sdp[q], sv[kk * 32 + 16 + p] * sdp[q], gv1, gv2);
+      scr[p] = gv1; scr[16 + p] = gv2;
+      __syncwarp();
+      const double dv = div_finish(t, scr, scr + 16);
+      if (k < nlev) sdiv[q] = dv;
+      __syncwarp();
+    }
+    __syncthreads();
+    if (tid < 16) {
+      double sum = 0.0;
+      for (int k = 0; k < nlev; k++) { sum = sum + sdiv[k * 16 + tid]; seta[(k + 1) * 16 + tid] = sum; }
+      for (int k = 0; k < nlev - 1; k++) seta[(k + 1) * 16 + tid] = c_hybi[k + 1] * sum - seta[(k + 1) * 16 + tid];
+      seta[tid] = 0.0;
+      seta[nlev * 16 + tid] = 0.0;
+    }
+    __syncthreads();
+  }
   const double fcor = A.geo.fcor[(size_t)ie * 16 + p], spheremp = A.geo.spheremp[(size_t)ie * 16 + p];
   const double gps1 = A.geo.gradphis[(size_t)ie * 32 + p], gps2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
   const double s1 = A.scale1, s2 = A.scale2, s3 = A.scale3, dt2 = A.dt2;
@@ -307,13 +331,43 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       if (FORM == 1) div_v_theta = nc;
       else div_v_theta = div_finish(t, scr + 64, scr + 80) / 2 + nc / 2;
     }
-    const double theta_tens = (-div_v_theta) * s1;                                  // theta_vadv = 0 (rsplit>0)
+    // vertically Eulerian terms (PA:1252-1302); all zero for rsplit > 0 (PA:1219-1225)
+    double theta_vadv = 0.0, w_vadv_k = 0.0, phi_vadv_k = 0.0, w_vadv_b = 0.0, vv1 = 0.0, vv2 = 0.0, deta = 0.0;
+    if (VADV) {
+      const double eta_k = seta[q], eta_k1 = seta[q + 16];
+      const int km = k > 0 ? k - 1 : 0, kp = k < nlev - 1 ? k + 1 : nlev - 1;
+      const double phm = (sphi[q] + sphi[q + 16]) / 2;                               // PA:1183
+      // preq_vertadv_v1 (prim_si_mod.F90:119-147): the one-sided end formulas are the general one with
+      // eta_dot = 0 at the model top and bottom
+      const double facp = div_fast(0.5 * eta_k1, dp), facm = div_fast(0.5 * eta_k, dp);
+      vv1 = facp * (sv[kp * 32 + p] - v1) + facm * (v1 - sv[km * 32 + p]);
+      vv2 = facp * (sv[kp * 32 + 16 + p] - v2) + facm * (v2 - sv[km * 32 + 16 + p]);
+      // theta at the interfaces k and k+1, energy-conserving average (PA:1268-1272); zero at top and bottom
+      double thi_k = 0.0, thi_k1 = 0.0, tmp_m = 0.0;
+      if (k > 0) {
+        const double phm_m = (sphi[q - 16] + sphi[q]) / 2;
+        thi_k = div_fast(div_fast(-mu_k * (phm - phm_m), exner - sexn[q - 16]), CP);
+        tmp_m = ((seta[q - 16] + eta_k) / 2) * (wk - sw[q - 16]);                     // temp(k-1), PA:1279
+        phi_vadv_k = div_fast(eta_k * (phm - phm_m), dpi_k);                           // PA:1289,1298
+      }
+      if (k < nlev - 1) {
+        const double phm_p = (sphi[q + 16] + sphi[q + 32]) / 2;
+        thi_k1 = div_fast(div_fast(-mu_k1 * (phm_p - phm), sexn[q + 16] - exner), CP);
+      }
+      const double tmp_k = ((eta_k + eta_k1) / 2) * (wk1 - wk);
+      theta_vadv = eta_k1 * thi_k1 - eta_k * thi_k;                                   // PA:1283-1284
+      w_vadv_k = div_fast(k > 0 ? (tmp_m + tmp_k) / 2 : tmp_k, dpi_k);                // PA:1288,1291,1297
+      w_vadv_b = div_fast(tmp_k, dp);                                                 // interface nlevp: dp3d_i = dp3d(nlev)
+      deta = eta_k1 - eta_k;
+      if (ACCUM && act) A.der.eta_dot_dpdn[(size_t)ie * 16 * nlevp + q] += A.eta_ave_w * eta_k;   // PA:1309-1316
+    }
+    const double theta_tens = (-theta_vadv - div_v_theta) * s1;
 
     // w, phi tendencies at interface k  PA:1326-1344
     const double v_gradw = v1i_k * gw1_k + v2i_k * gw2_k;
-    const double w_tens = (-v_gradw) * s1 - s2 * G_GRAV * (1 - mu_k);
+    const double w_tens = (-w_vadv_k - v_gradw) * s1 - s2 * G_GRAV * (1 - mu_k);
     const double v_gradphi = v1i_k * gphi1_k + v2i_k * gphi2_k;
-    double phi_tens = (-v_gradphi) * s1 + s2 * G_GRAV * wk;
+    double phi_tens = (-phi_vadv_k - v_gradphi) * s1 + s2 * G_GRAV * wk;
     if (s1 != s2) phi_tens = phi_tens + (s1 - s2) * (v1i_k * gps1 + v2i_k * gps2) * c_hybi[k];
 
     // momentum PA:1404-1509
@@ -339,8 +393,8 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       mg1 = mg1 + CP * T0 * (gl1 - div_fast(ge1, exner));
       mg2 = mg2 + CP * T0 * (gl2 - div_fast(ge2, exner));
     }
-    const double vt1 = (v2 * (fcor + vort) - ke1 - mg1 - gp1 - wv1) * s1;           // PA:1495-1506 (v_vadv = 0)
-    const double vt2 = (-v1 * (fcor + vort) - ke2 - mg2 - gp2 - wv2) * s1;
+    const double vt1 = (-vv1 + v2 * (fcor + vort) - ke1 - mg1 - gp1 - wv1) * s1;    // PA:1495-1506
+    const double vt2 = (-vv2 - v1 * (fcor + vort) - ke2 - mg2 - gp2 - wv2) * s1;
 
     if (act) {
       // PA:1674-1690  X(np1) = spheremp*(scale3*X(nm1) + dt2*tens); reads of nm1 straight from HBM
@@ -349,7 +403,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       A.tens.th[gq] = spheremp * (s3 * m_th + dt2 * theta_tens);
       A.tens.w[gqi] = spheremp * (s3 * m_w + dt2 * w_tens);
       A.tens.phi[gqi] = spheremp * (s3 * m_phi + dt2 * phi_tens);
-      A.tens.dp[gq] = spheremp * (s3 * m_dp - s1 * dt2 * divdp);                    // eta_dot = 0
+      A.tens.dp[gq] = spheremp * (s3 * m_dp - s1 * dt2 * (VADV ? divdp + deta : divdp));   // PA:1693-1694
       if (accum) {
         sdiv[q] = divdp;
         A.der.vn0[gqv] += A.eta_ave_w * (v1 * dp);                                  // PA:1190
@@ -357,7 +411,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       }
       if (k == nlev - 1) {                                                          // PA:1349-1361, :1699
         const double v_gradw_b = v1 * gw1_k1 + v2 * gw2_k1;                         // v_i(nlevp) = v(nlev)
-        const double w_tens_b = (-v_gradw_b) * s1 - s1 * G_GRAV * (1 - mu_k1);
+        const double w_tens_b = (-w_vadv_b - v_gradw_b) * s1 - s1 * G_GRAV * (1 - mu_k1);
         A.tens.w[gqi + 16] = spheremp * (s3 * A.nm1.w[gqi + 16] + dt2 * w_tens_b);
       }
     }
@@ -392,23 +446,24 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   }
 }
 
-template <int FORM, bool PGRAD, bool ACCUM>
+template <int FORM, bool PGRAD, bool ACCUM, bool VADV>
 static void launch_caar_pre_t(const CaarArgs &A, cudaStream_t st)
 {
-  const size_t sm = caar_smem_bytes(A.prm.nlev);
+  const size_t sm = caar_smem_bytes(A.prm.nlev, VADV);
   static size_t configured = 0;
   if (sm > configured) {
-    cudaFuncSetAttribute(caar_pre_kernel<FORM, PGRAD, ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaFuncSetAttribute(caar_pre_kernel<FORM, PGRAD, ACCUM, VADV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     configured = sm;
   }
-  caar_pre_kernel<FORM, PGRAD, ACCUM><<<A.prm.nelem, CAAR_THREADS, sm, st>>>(A);
+  caar_pre_kernel<FORM, PGRAD, ACCUM, VADV><<<A.prm.nelem, CAAR_THREADS, sm, st>>>(A);
 }
 
 template <int FORM, bool PGRAD>
 static void launch_caar_pre_a(const CaarArgs &A, cudaStream_t st)
 {
-  if (A.eta_ave_w != 0.0) launch_caar_pre_t<FORM, PGRAD, true>(A, st);
-  else launch_caar_pre_t<FORM, PGRAD, false>(A, st);
+  const bool acc = A.eta_ave_w != 0.0, vadv = A.prm.rsplit == 0;
+  if (vadv) { acc ? launch_caar_pre_t<FORM, PGRAD, true, true>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, true>(A, st); }
+  else { acc ? launch_caar_pre_t<FORM, PGRAD, true, false>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, false>(A, st); }
 }
 
 void launch_caar_pre(const CaarArgs &A, cudaStream_t st)
@@ -1376,6 +1431,33 @@ __global__ void __launch_bounds__(DSS_THREADS) combo_kernel(const ComboArgs A)
 void launch_combo(const ComboArgs &A, cudaStream_t st)
 {
   combo_kernel<<<A.prm.nelem, DSS_THREADS, 0, st>>>(A);
+}
+
+// applyCAMforcing_dynamics (PA:517-541), standalone HOMME variant (FM(:,:,3,:) forces w_i): one CTA per
+// element.  fm is derived%FM(np,np,3,nlev,ie), fvtheta derived%FVTheta(np,np,nlev,ie), fphi FPHI(np,np,nlevp,ie).
+__global__ void __launch_bounds__(256) forcing_kernel(StatePtrs s, const double *fm, const double *fvtheta,
+                                                      const double *fphi, Geo geo, double dt, int nlev)
+{
+  const int ie = blockIdx.x, p = threadIdx.x & 15, nlevp = nlev + 1;
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  const double *f = fm + (size_t)ie * 48 * nlev;
+  for (int k = threadIdx.x >> 4; k < nlev; k += 16) {
+    const int q = k * 16 + p;
+    s.th[em + q] = s.th[em + q] + dt * fvtheta[em + q];
+    s.phi[ei + q] = s.phi[ei + q] + dt * fphi[ei + q];
+    const double v1 = s.v[ev + k * 32 + p] + dt * f[k * 48 + p];
+    const double v2 = s.v[ev + k * 32 + 16 + p] + dt * f[k * 48 + 16 + p];
+    s.v[ev + k * 32 + p] = v1;
+    s.v[ev + k * 32 + 16 + p] = v2;
+    s.w[ei + q] = s.w[ei + q] + dt * f[k * 48 + 32 + p];
+    if (k == nlev - 1)
+      s.w[ei + (size_t)nlev * 16 + p] = (v1 * geo.gradphis[(size_t)ie * 32 + p] + v2 * geo.gradphis[(size_t)ie * 32 + 16 + p]) / G_GRAV;
+  }
+}
+void launch_forcing(const StatePtrs &s, const double *fm, const double *fvtheta, const double *fphi, const Geo &geo,
+                    double dt, int nelem, int nlev, cudaStream_t st)
+{
+  forcing_kernel<<<nelem, 256, 0, st>>>(s, fm, fvtheta, fphi, geo, dt, nlev);
 }
 
 // FP64 FMA peak probe: 8 independent DFMA chains per thread, 1024 threads per CTA, 2 CTAs per SM

@@ -102,7 +102,7 @@ class ThetaLDycore:
             _cd(p.nu), _cd(p.nu_p), _cd(0.0), _cd(p.nu_s), _cd(p.nu_div), _cd(p.nu_top),
             _ci(p.hypervis_order), _ci(p.hypervis_subcycle), _ci(p.hypervis_subcycle_tom),
             _cd(p.hypervis_scaling), _cd(0.0), _cd(0.0),
-            _ci(-1), _ci(p.theta_advect_form), _ci(0), _ci(0), _ci(1), _ci(0),
+            _ci(getattr(p, 'ftype', -1)), _ci(p.theta_advect_form), _ci(0), _ci(0), _ci(1), _ci(0),
             _ci(0), _ci(0), byref(name),
             _ci(p.rsplit * p.qsplit), _ci(p.qsplit), _cd(grid.rearth), _cd(1.0 / grid.rearth), _ci(1),
             _ci(p.pgrad_correction), _cd(p.dp3d_thresh), _cd(p.vtheta_thresh), _ci(0), _ci(0),
@@ -205,6 +205,19 @@ class ThetaLDycore:
         self.L.prim_run_subcycle_c(_cd(dt), byref(a), byref(b), byref(c), byref(d), _ci(0), _ci(0))
         self._check()
         return a.value, b.value, c.value, d.value
+
+    def push_forcing(self, fm, fvtheta, fphi):
+        """push_forcing_to_c: derived%FM [ie][k][3][16], FVTheta [ie][k][16], FPHI [ie][k<=nlev][16] (FT, FQ unused)."""
+        for a in (fm, fvtheta, fphi):
+            assert a.flags["C_CONTIGUOUS"] and a.dtype == np.float64
+        self.L.push_forcing_to_c(c_void_p(fm.ctypes.data), c_void_p(fvtheta.ctypes.data), None,
+                                 c_void_p(fphi.ctypes.data), None)
+        self._check()
+
+    def apply_forcing_dynamics(self, nt, dt):
+        """applyCAMforcing_dynamics (prim_advance_mod.F90:517-541) on time level nt (0-based)."""
+        self.L.apply_cam_forcing_dynamics_c(_ci(nt), _cd(dt))
+        self._check()
 
     def init_time_level(self, nm1, n0, np1, nstep=0, nstep0=0):
         """init_time_level_c with 1-BASED levels like the Fortran caller (prim_driver_mod.F90:196)."""

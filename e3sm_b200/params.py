@@ -30,6 +30,7 @@ class SimParams:
     vtheta_thresh: float = 100.0        # :98
     tom_sponge_start: float = 0.0
     u_perturb: float = 1.0
+    ftype: int = -1                     # forcing algorithm; 0 / 2 apply the pushed forcing per model step
     vert_remap_u_alg: int = 1           # PPM, mirrored ghost cells (vertremap_base.F90:509-512); 10/11 also built
 
     @property

@@ -80,8 +80,13 @@ void init_boundary_exchanges_c(void);
 void initialize_dp3d_from_ps_c(void);
 
 /* ---- run time: theta_f2c_mod.F90:189-236; impl H/src/share/cxx/prim_driver.cpp:60-181 */
+/* derived%FM(np,np,3,nlev,nelemd), FVTheta(np,np,nlev,nelemd), FT (unused), FPHI(np,np,nlevp,nelemd), FQ (qsize = 0:
+ * unused).  prim_run_subcycle_c applies them to time level n0 with dt_remap when ftype is 0 or 2
+ * (prim_driver.cpp:117-125 -> applyCAMforcing_dynamics, prim_advance_mod.F90:517-541, standalone variant). */
 void push_forcing_to_c(const double *fm, const double *fvtheta, const double *ft,
                        const double *fphi, const double *fq);
+/* addition: applyCAMforcing_dynamics alone on time level *nt (0-based), for parity tests */
+void apply_cam_forcing_dynamics_c(const int *nt, const double *dt);
 /* nstep, nm1, n0, np1 are pure OUTPUTS (never read): the library advances its own TimeLevel, set by
  * init_time_level_c, and reports it 0-BASED as prim_driver.cpp:174-178 does; the Fortran caller adds 1
  * (prim_driver_mod.F90:554-560).  One call = rsplit prim_steps (each: zero vn0/omega_p/eta_dot_dpdn, then

@@ -130,6 +130,10 @@ class Oracle:
         self.lib.orc_prim_advance_exp(byref(self.c), c_int(self.params.tstep_type), c_double(dt), c_int(nm1),
                                       c_int(n0), c_int(np1), c_int(self.params.qsplit))
 
+    def apply_forcing_dynamics(self, np1, dt, fm, fvtheta, fphi):
+        """applyCAMforcing_dynamics (PA:517-541); fm [ie][k][3][16], fvtheta [ie][k][16], fphi [ie][k<=nlev][16]."""
+        self.lib.orc_apply_forcing_dynamics(byref(self.c), c_int(np1), c_double(dt), _p(fm), _p(fvtheta), _p(fphi))
+
     @property
     def error_flag(self):
         return self.c.error_flag

@@ -881,6 +881,30 @@ void orc_dirk(orc_ctx *c, int nm1, double alphadt_nm1, int n0, double alphadt_n0
   if (itererr) *itererr = fmin(max_re, max_de);
 }
 
+/* applyCAMforcing_dynamics, PA:517-541 (standalone HOMME: the #ifndef CAM branch forces w_i with FM(:,:,3,:)).
+ * fm = derived%FM(np,np,3,nlev,ie), fvtheta = FVTheta(np,np,nlev,ie), fphi = FPHI(np,np,nlevp,ie). */
+void orc_apply_forcing_dynamics(orc_ctx *c, int np1, double dt, const double *fm, const double *fvtheta,
+                                const double *fphi)
+{
+  const int nlev = c->nlev, nlevp = nlev + 1;
+  for (int ie = 0; ie < c->nelem; ie++) {
+    double *v = c->v + off_v(c, ie, np1), *th = c->vtheta_dp + off_m(c, ie, np1);
+    double *w = c->w_i + off_i(c, ie, np1), *ph = c->phinh_i + off_i(c, ie, np1);
+    const double *f = fm + (size_t)ie*48*nlev, *ft = fvtheta + (size_t)ie*16*nlev, *fp = fphi + (size_t)ie*16*nlevp;
+    const double *gradphis = c->gradphis + (size_t)ie*32;
+    for (int k = 0; k < nlev; k++)
+      for (int p = 0; p < NPSQ; p++) {
+        th[k*16 + p] = th[k*16 + p] + dt * ft[k*16 + p];
+        ph[k*16 + p] = ph[k*16 + p] + dt * fp[k*16 + p];
+        v[k*32 + p]      = v[k*32 + p]      + dt * f[k*48 + p];
+        v[k*32 + 16 + p] = v[k*32 + 16 + p] + dt * f[k*48 + 16 + p];
+        w[k*16 + p] = w[k*16 + p] + dt * f[k*48 + 32 + p];
+      }
+    for (int p = 0; p < NPSQ; p++)
+      w[nlev*16 + p] = (v[(nlev-1)*32 + p] * gradphis[p] + v[(nlev-1)*32 + 16 + p] * gradphis[16 + p]) / g_;
+  }
+}
+
 /* ---------------- hyperviscosity ---------------- */
 /* stens layout (np,np,nlev,4,ie): dp3d, theta, w, phi ; vtens (np,np,2,nlev,ie).
  * scratch1 = [ie][ vtens 32*nlev | stens 4*16*nlev ] so that one DSS call covers 6*nlev layers. */

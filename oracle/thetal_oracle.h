@@ -90,4 +90,7 @@ void orc_vlaplace_sphere_wk(const orc_ctx *c, int ie, const double *v, int var_c
 #ifdef __cplusplus
 }
 #endif
+/* PA:517-541 */
+void orc_apply_forcing_dynamics(orc_ctx *c, int np1, double dt, const double *fm, const double *fvtheta,
+                                const double *fphi);
 #endif

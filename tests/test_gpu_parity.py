@@ -444,3 +444,73 @@ def test_bad_state_is_fatal(case_c1, parity_state_c1):
         d.close()
     finally:
         L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(1)))
+
+
+# ---------------------------------------------------------------- rsplit = 0 (a13) and forcing (N2)
+@pytest.mark.parametrize("np1,nm1,n0", [(2, 0, 1), (2, 1, 1), (0, 1, 1)])
+@pytest.mark.parametrize("form,pgrad,eta_ave_w", [(0, 0, 0.25), (1, 1, 0.0), (2, 0, 1.0)])
+def test_caar_vertically_eulerian(case_c1, parity_state_c1, np1, nm1, n0, form, pgrad, eta_ave_w):
+    """rsplit = 0: eta_dot_dpdn, preq_vertadv_v1 and the theta/w/phi vertical advection terms
+    (prim_advance_mod.F90:1227-1316, prim_si_mod.F90:94-148), accumulated derived%eta_dot_dpdn included."""
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    st = distinct_levels(parity_state_c1, phis, gradphis)
+    p, o, so, d = make_pair(case_c1, st, theta_advect_form=form, pgrad_correction=pgrad, rsplit=0)
+    args = (np1, nm1, n0, 37.5, eta_ave_w, 1.0, 0.0, 1.0)
+    o.compute_andor_apply_rhs(*args)
+    d.compute_andor_apply_rhs(*args)
+    assert_state_close(d.get_state(), so, np1, TOL, f"caar rsplit=0 np1={np1} nm1={nm1} n0={n0} form={form}")
+    vn0, eta, om = d.get_derived()
+    assert rel_l2(vn0, o.vn0) <= TOL
+    if eta_ave_w != 0:
+        assert np.abs(o.eta_dot_dpdn).max() > 0
+        assert rel_l2(eta, o.eta_dot_dpdn) <= 1e-9        # differences of prefix sums of div(v dp)
+    d.close()
+
+
+@pytest.mark.parametrize("tt,dt", [(9, 300.0), (10, 300.0), (5, 1.0)])     # tt5 is fully explicit: acoustic time step
+def test_steps_vertically_eulerian(case_c1, parity_state_c1, tt, dt):
+    """three dynamics steps with rsplit = 0 through prim_run_subcycle_c: one prim_step per call, no remap of the
+    dynamics (prim_driver.cpp:79-83, vertical_remap with rsplit = 0)"""
+    p, o, so, d = make_pair(case_c1, parity_state_c1.copy(), rsplit=0, tstep_type=tt, tstep=dt)
+    nm1, n0, np1 = 0, 1, 2
+    for call in range(3):
+        o.vn0[:] = 0; o.omega_p[:] = 0; o.eta_dot_dpdn[:] = 0
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        assert o.error_flag == 0
+        nm1, n0, np1 = n0, np1, nm1
+        nstep, c_nm1, c_n0, c_np1 = d.prim_run_subcycle(p.tstep)
+        assert nstep == call + 1 and (c_nm1, c_n0, c_np1) == (nm1, n0, np1)
+    assert o.error_flag == 0
+    assert_state_close(d.get_state(), so, n0, 1e-9, f"rsplit=0 steps tt{tt}")
+    vn0, eta, om = d.get_derived()
+    assert rel_l2(eta, o.eta_dot_dpdn) <= 1e-8
+    d.close()
+
+
+def test_forcing_through_prim_run_subcycle(case_c1, parity_state_c1):
+    """push_forcing_to_c + ftype 0: prim_run_subcycle_c applies applyCAMforcing_dynamics to time level n0 with
+    dt_remap = tstep*rsplit*qsplit before its dynamics steps (prim_driver.cpp:117-125, PA:517-541)"""
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    p, o, so, d = make_pair(case_c1, parity_state_c1.copy(), ftype=0)
+    rng = np.random.default_rng(7)
+    n, nlev = grid.nelem, hv.nlev
+    from e3sm_b200.initial import make_c0
+    fm = np.ascontiguousarray(1e-5 * make_c0(grid, rng.uniform(-1, 1, (n, nlev, 3, 16))))
+    fvt = np.ascontiguousarray(1e-3 * so.vtheta_dp[:, 0] / 300.0 * make_c0(grid, rng.uniform(-1, 1, (n, nlev, 16))))
+    fphi = np.ascontiguousarray(1e-3 * make_c0(grid, rng.uniform(-1, 1, (n, nlev + 1, 16))))
+    d.push_forcing(fm, fvt, fphi)
+    nm1, n0, np1 = 0, 1, 2
+    for call in range(2):
+        o.apply_forcing_dynamics(n0, p.tstep * p.rsplit * p.qsplit, fm, fvt, fphi)
+        for r in range(p.rsplit * p.qsplit):
+            o.prim_advance_exp(p.tstep, nm1, n0, np1)
+            nm1, n0, np1 = n0, np1, nm1
+        assert o.vertical_remap(n0, p.vert_remap_u_alg) == 0
+        d.prim_run_subcycle(p.tstep)
+    assert o.error_flag == 0
+    assert_state_close(d.get_state(), so, n0, 1e-9, "forcing + prim_run_subcycle")
+    # the forcing kernel alone
+    o.apply_forcing_dynamics(n0, 123.0, fm, fvt, fphi)
+    d.apply_forcing_dynamics(n0, 123.0)
+    assert_state_close(d.get_state(), so, n0, 1e-9, "applyCAMforcing_dynamics")
+    d.close()
