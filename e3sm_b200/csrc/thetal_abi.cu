@@ -100,8 +100,10 @@ Session S;
 
 void fail(int code, const std::string &msg)
 {
-  S.last_error = code;
-  S.last_msg = msg;
+  if (S.last_error == 0) {      // latched: the FIRST failure is what thetal_b200_last_error reports until it is cleared
+    S.last_error = code;
+    S.last_msg = msg;
+  }
   fprintf(stderr, "thetal_b200: ERROR %d: %s\n", code, msg.c_str());
   if (S.abort_on_error) abort();
 }
@@ -376,7 +378,9 @@ void init_simulation_params_c(const int *remap_alg, const int *limiter_option, c
   CHECK_IN("do_3d_turbulence", *do_3d_turbulence, {0});
   FAIL_IF(!(*nu_p > 0) || !(*nu > 0) || !(*nu_div > 0), 3, "nu, nu_p, nu_div must be > 0");
   FAIL_IF(!(*dp3d_thresh > 0) || !(*vtheta_thresh > 0), 3, "dp3d_thresh, vtheta_thresh must be > 0");
-  FAIL_IF(*hypervis_scaling != 0.0, 3, "tensor hyperviscosity (hypervis_scaling != 0) is a next-row item (SURVEY 8f N4)");
+  FAIL_IF(*hypervis_scaling < 0.0, 3, "hypervis_scaling must be >= 0");
+  // tensor hyperviscosity needs the Cartesian vector laplacian, which has no nu_div (derivative_mod.F90:1146-1150)
+  FAIL_IF(*hypervis_scaling > 0.0 && *nu_div != *nu, 3, "ERROR: tensorHV can not be used with nu_div/=nu");
   FAIL_IF(*laplace_scaling != 0.0, 3, "laplace_scaling != 0 not supported");
   FAIL_IF(*dcmip16_mu != 0.0, 3, "dcmip16_mu != 0 not supported");
   FAIL_IF(*rsplit < 0, 3, "rsplit must be >= 0 (0 = vertically Eulerian, PA:1227-1303)");
@@ -395,7 +399,7 @@ void init_simulation_params_c(const int *remap_alg, const int *limiter_option, c
   p.rsplit = *rsplit; p.qsplit = dtf; p.tstep_type = *time_step_type;
   p.theta_advect_form = *theta_adv_form; p.pgrad_correction = *pgrad_correction;
   p.hypervis_subcycle = *hypervis_subcycle; p.hypervis_subcycle_tom = *hypervis_subcycle_tom;
-  p.hypervis_scaling_on = 0;
+  p.hypervis_scaling_on = *hypervis_scaling > 0.0 ? 1 : 0;
   p.nu = *nu; p.nu_div = *nu_div; p.nu_p = *nu_p; p.nu_s = *nu_s; p.nu_top = *nu_top;
   p.dp3d_thresh = *dp3d_thresh; p.vtheta_thresh = *vtheta_thresh;
   p.rearth_inv = *laplacian_rigid_factor;     // == 1/scale_factor on the sphere (namelist_mod.F90:1045-1047)

@@ -1147,6 +1147,56 @@ __device__ __forceinline__ void laplace_level(const Pt &t, const PtW &w, double 
 }
 
 
+// Tensor hyperviscosity (hypervis_scaling > 0): weak laplacians of NF scalar tiles with the
+// gradient multiplied by elem%tensorVisc before the weak divergence (laplace_sphere_wk with var_coef,
+// DM:1090-1117).  tv[b*2+a] = tensorVisc(i,j,a,b).  Uses 3*NF scratch tiles; all 16 lanes call it together.
+template <int NF, bool TENSOR>
+__device__ __forceinline__ void laplace_scalars(const Pt &t, const PtW &w, const double tv[4], double *scr,
+                                                const double *s_in, double *lap_s)
+{
+  const int p = t.p;
+#pragma unroll
+  for (int f = 0; f < NF; f++) scr[f * 16 + p] = s_in[f];
+  __syncwarp();
+#pragma unroll
+  for (int f = 0; f < NF; f++) {
+    double g1, g2;
+    gradient_sphere(t, scr + f * 16, g1, g2);
+    if (TENSOR) {
+      const double o1 = g1, o2 = g2;
+      g1 = o1 * tv[0] + o2 * tv[2];
+      g2 = o1 * tv[1] + o2 * tv[3];
+    }
+    scr[(NF + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[0] * g1 + t.Dinv[2] * g2);      // DM:814-819
+    scr[(NF + 2 * f + 1) * 16 + p] = w.spheremp * (t.Dinv[1] * g1 + t.Dinv[3] * g2);
+  }
+  __syncwarp();
+#pragma unroll
+  for (int f = 0; f < NF; f++) {                                                      // DM:821-833
+    const double *T1 = scr + (NF + 2 * f) * 16 + t.b * 4, *T2 = scr + (NF + 2 * f + 1) * 16 + t.a;
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc = acc - (T1[j] * w.dta[j] + T2[4 * j] * w.dtb[j]) * t.sfi;
+    lap_s[f] = acc;
+  }
+  __syncwarp();
+}
+
+// vlaplace_sphere_wk_cartesian (DM:1164-1208): lat-lon -> three Cartesian components, tensor laplacian of each,
+// back to lat-lon, plus the rigid-rotation correction.  s2c[c2*3+c3] = vec_sphere2cart(i,j,c3,c2).
+__device__ __forceinline__ void vlaplace_cartesian(const Pt &t, const PtW &w, const double tv[4], const double s2c[6],
+                                                   double *scr, double v1, double v2, double &lap_v1, double &lap_v2)
+{
+  double dum[3], out[3];
+#pragma unroll
+  for (int c = 0; c < 3; c++) dum[c] = s2c[c] * v1 + s2c[3 + c] * v2;
+  laplace_scalars<3, true>(t, w, tv, scr, dum, out);
+  lap_v1 = out[0] * s2c[0] + out[1] * s2c[1] + out[2] * s2c[2];
+  lap_v2 = out[0] * s2c[3] + out[1] * s2c[4] + out[2] * s2c[5];
+  lap_v1 = lap_v1 + 2 * w.spheremp * v1 * w.lrf2;
+  lap_v2 = lap_v2 + 2 * w.spheremp * v2 * w.lrf2;
+}
+
 __host__ __device__ inline size_t hv_smem_bytes() { return sizeof(double) * (HV_THREADS / 16) * HV_SLOTS * 16; }
 
 // pass 1 (PA:629-636 + VT:93-107): laplacians of (state - reference state) -> tout
@@ -1207,6 +1257,7 @@ __global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace1_kernel(const HvArgs
 }
 
 // pass 2 (VT:134-164 + PA:657-663): DSS(tin) * rspheremp -> laplacian again -> * (-nu) -> tout
+template <bool TENSOR>
 __global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace2_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
@@ -1228,6 +1279,13 @@ __global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace2_kernel(const HvArgs
     if (tid == 2) prefetch_l2(A.tin.th + em, (unsigned)(sm_ * 8));
     if (tid == 3) prefetch_l2(A.tin.w + ei, (unsigned)(si * 8));
     if (tid == 4) prefetch_l2(A.tin.phi + ei, (unsigned)(si * 8));
+  }
+  double tv[4] = {0, 0, 0, 0}, s2c[6] = {0, 0, 0, 0, 0, 0};
+  if (TENSOR) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) tv[q] = A.geo.tensorvisc[(size_t)ie * 64 + q * 16 + p];
+#pragma unroll
+    for (int q = 0; q < 6; q++) s2c[q] = A.geo.vec_sph2cart[(size_t)ie * 96 + q * 16 + p];
   }
   const int niter = (nlev + KS - 1) / KS;
   double n_s[6];
@@ -1252,7 +1310,12 @@ __global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace2_kernel(const HvArgs
     s[0] = n_s[0]; s[1] = n_s[1]; s[2] = n_s[2]; s[3] = n_s[3];
     const double v1 = n_s[4], v2 = n_s[5];
     if (it + 1 < niter) gather(it + 1);        // next level's DSS sums are requested before this level's laplacians
-    laplace_level(t, w, scr, A.nu_ratio, s, v1, v2, lap, l1, l2);
+    if (TENSOR) {                              // VT:145-163 with var_coef: tensor on the second laplacian only
+      laplace_scalars<4, true>(t, w, tv, scr, s, lap);
+      vlaplace_cartesian(t, w, tv, s2c, scr, v1, v2, l1, l2);
+    } else {
+      laplace_level(t, w, scr, A.nu_ratio, s, v1, v2, lap, l1, l2);
+    }
     if (act) {
       A.tout.dp[em + q] = -A.prm.nu_p * lap[0]; A.tout.th[em + q] = -A.prm.nu * lap[1];
       A.tout.w[ei + q] = -A.prm.nu * lap[2]; A.tout.phi[ei + q] = -A.prm.nu_s * lap[3];
@@ -1360,7 +1423,10 @@ void launch_hv(int which, const HvArgs &A, cudaStream_t st)
   if (nb <= 0) return;
   switch (which) {
     case 0: hv_laplace1_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
-    case 1: hv_laplace2_kernel<<<nb, HV_THREADS, sm, st>>>(A); break;
+    case 1:
+      if (A.prm.hypervis_scaling_on) hv_laplace2_kernel<true><<<nb, HV_THREADS, sm, st>>>(A);
+      else hv_laplace2_kernel<false><<<nb, HV_THREADS, sm, st>>>(A);
+      break;
     case 2: hv_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
     case 3: hv_sponge_laplace_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
     case 4: hv_sponge_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;

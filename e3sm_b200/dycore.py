@@ -148,8 +148,10 @@ class ThetaLDycore:
 
     # ------------------------------------------------------------------ helpers
     def _check(self):
-        if self.L.thetal_b200_last_error() != 0:
-            raise RuntimeError("libthetal_b200: " + self.L.thetal_b200_last_error_msg().decode())
+        if self.L.thetal_b200_last_error() != 0:      # latched (abort_on_error = 0): report the first failure, then clear
+            msg = self.L.thetal_b200_last_error_msg().decode()
+            self.L.thetal_b200_clear_error()
+            raise RuntimeError("libthetal_b200: " + msg)
 
     def set_state(self, st):
         """init_elements_states_c: host (flat Fortran layout) -> device."""
@@ -290,11 +292,11 @@ def build_case(params, hv_ref_profiles=None, part=None, rank=0):
     hv = HVCoord.from_table(params.nlev)
     hvr = params.hv_ref_profiles if hv_ref_profiles is None else hv_ref_profiles
     if part is None:
-        grid = CubedSphere(params.ne)
+        grid = CubedSphere(params.ne, hypervis_scaling=params.hypervis_scaling)
         st, phis = jw_baroclinic(grid, hv, params.u_perturb)
         gradphis, theta_ref, dp_ref, phi_ref = model_init2(grid, hv, st, phis, hvr)
         return grid, hv, st, phis, gradphis, (theta_ref, dp_ref, phi_ref)
-    grid = CubedSphere(params.ne, order=part.order)
+    grid = CubedSphere(params.ne, order=part.order, hypervis_scaling=params.hypervis_scaling)
     e0, e1 = part.local_range(rank)
     gradphis_all = make_c0(grid, gradient_sphere(grid, jw_phis(grid)))
     loc = grid.local_view(e0, e1)

@@ -235,8 +235,9 @@ class CubedSphere:
     memory layout per element (see module docstring).
     """
 
-    def __init__(self, ne, order=None, rearth=REARTH):
+    def __init__(self, ne, order=None, rearth=REARTH, hypervis_scaling=0.0):
         self.ne = ne
+        self.hypervis_scaling = float(hypervis_scaling)
         nelem = 6 * ne * ne
         gnum = np.arange(nelem) if order is None else np.asarray(order, dtype=np.int64)
         assert np.array_equal(np.sort(gnum), np.arange(nelem))
@@ -307,6 +308,15 @@ class CubedSphere:
         metinv[..., 0, 1] = -met12 / (detD * detD)
         metinv[..., 1, 0] = -met12 / (detD * detD)
         metinv[..., 1, 1] = met11 / (detD * detD)
+        # tensor for the resolution-aware hyperviscosity, from the UNCORRECTED D and metinv (cube_mod.F90:313-428
+        # runs before the area correction :458-494):  V = (D E) diag(lamStar_i^2 eig_i) (D E)^T with
+        # metinv = E diag(eig) E^T and lamStar_i = eig_i^(-hypervis_scaling/4) rearth^2
+        Vt = None
+        if self.hypervis_scaling != 0.0:
+            eig, E = np.linalg.eigh(metinv)                              # [e,j,i,2], [e,j,i,2,2]
+            lam = eig ** (1.0 - self.hypervis_scaling / 2.0) * rearth ** 4
+            DE = np.einsum("ejiab,ejibc->ejiac", D, E)
+            Vt = np.einsum("ejiac,ejic,ejibc->ejiab", DE, lam, DE)      # [e,j,i,a,b] = tensorVisc(i,j,a,b)
         sa = np.sqrt(alpha)[:, None, None, None, None]
         al = alpha[:, None, None]
         inner = (slice(None), slice(1, NP - 1), slice(1, NP - 1))
@@ -334,6 +344,20 @@ class CubedSphere:
         self.node_id, self.dss_src, self.edge_nbrs = build_dss_tables(labels)
         self.nnodes = int(self.node_id.max()) + 1
         self.rspheremp = 1.0 / dss_numpy(self.spheremp, self.dss_src)    # mass_matrix_mod.F90:100-114
+        if Vt is not None:
+            # dss_hvtensor (global_norms_mod.F90:415-486): mass-weighted DSS of every component, then the
+            # bilinear function of the four (now continuous) corner values inside each element
+            V = Vt.reshape(nelem, 16, 2, 2)
+            x = np.tile(pts, NP)                                         # x(p) = pts[i], y(p) = pts[j], p = j*4 + i
+            y = np.repeat(pts, NP)
+            out = np.zeros((nelem, 2, 2, 16))                            # [e,b,a,p]
+            for a in range(2):
+                for b in range(2):
+                    z = dss_numpy(V[:, :, a, b] * self.spheremp, self.dss_src) * self.rspheremp
+                    sw, se, nw, ne_ = z[:, 0:1], z[:, 3:4], z[:, 12:13], z[:, 15:16]
+                    out[:, b, a, :] = 0.25 * ((1.0 - x) * (1.0 - y) * sw + (1.0 - x) * (y + 1.0) * nw
+                                              + (x + 1.0) * (1.0 - y) * se + (x + 1.0) * (y + 1.0) * ne_)
+            self.tensorvisc = np.ascontiguousarray(out)
 
     def local_view(self, e0, e1):
         """Per-element arrays of the storage slice [e0:e1) (what one rank of the SFC partition owns)."""

@@ -72,7 +72,7 @@ class Oracle:
         c.hypervis_subcycle_tom = params.hypervis_subcycle_tom
         nst, nlev_tom = hv.nu_scale_top(params.tom_sponge_start)
         c.nlev_tom = nlev_tom
-        c.hypervis_scaling_on = 0
+        c.hypervis_scaling_on = 1 if params.hypervis_scaling > 0 else 0
         c.hv_theta_correction = 0
         c.nu, c.nu_div, c.nu_p, c.nu_s, c.nu_top = params.nu, params.nu_div, params.nu_p, params.nu_s, params.nu_top
         c.dp3d_thresh, c.vtheta_thresh = params.dp3d_thresh, params.vtheta_thresh

@@ -96,6 +96,43 @@ def test_hypervis(case_c1, parity_state_c1, hvs, tom, nu_div_fac):
     d.close()
 
 
+@pytest.mark.parametrize("hvs", [1, 2])
+def test_hypervis_tensor(hvs):
+    """tensor hyperviscosity (hypervis_scaling = 3: tensorVisc from cube_mod.F90:313-428 + dss_hvtensor, var_coef
+    on the second laplacian only, Cartesian vector laplacian; viscosity_theta.F90:147-161, derivative_mod.F90:
+    1090-1117,1164-1208) on a perturbed spun-up state"""
+    from e3sm_b200.dycore import build_case
+    from e3sm_b200.params import config
+    p = config("C1").with_(hypervis_scaling=3.0, nu=3.4e-8, nu_p=3.4e-8, nu_s=3.4e-8, nu_div=3.4e-8, hypervis_subcycle=hvs)
+    case = (p,) + build_case(p)
+    assert np.abs(case[1].tensorvisc).max() > 0
+    st = spun_up_state(case, nsteps=4)
+    p, o, so, d = make_pair(case, st)
+    o.advance_hypervis(2, 600.0, 1.0)
+    d.advance_hypervis(2, 600.0, 1.0)
+    assert_state_close(d.get_state(), so, 2, TOL, f"tensor hypervis hvs={hvs}")
+    # the operator really acted
+    assert rel_l2(so.v[:, 2], st.v[:, 2]) > 1e-8
+    d.close()
+
+
+def test_tensor_hypervis_rejects_nu_div(case_c1):
+    """derivative_mod.F90:1146-1150: tensorHV can not be used with nu_div /= nu"""
+    import ctypes
+    from e3sm_b200 import lib
+    from e3sm_b200.dycore import ThetaLDycore
+    p, grid, hv, st, phis, gradphis, refs = case_c1
+    L = lib.load()
+    L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(0)))
+    try:
+        with pytest.raises(RuntimeError, match="tensorHV can not be used"):
+            ThetaLDycore(grid, hv, p.with_(hypervis_scaling=3.0, nu_div=2 * p.nu), phis, gradphis, refs)
+    finally:
+        L.thetal_b200_clear_error()
+        L.thetal_b200_set_abort_on_error(ctypes.byref(ctypes.c_int(1)))
+        L.finalize_hommexx_session()
+
+
 @pytest.mark.parametrize("tt", [9, 10, 7, 5, 4, 1])
 def test_one_step(case_c1, parity_state_c1, tt):
     """one full prim_advance_exp: rel-L2 <= 1e-10 per prognostic (north star)"""
@@ -134,7 +171,12 @@ def test_ten_steps(case_c1):
                                       ("C2", {"tstep_type": 7, "theta_advect_form": 2, "pgrad_correction": 1}),
                                       # the EAMxx option set short of the tensor hyperviscosity (namelist_defaults_eamxx.xml:925-997)
                                       ("C2", {"hv_ref_profiles": 6, "theta_advect_form": 1, "pgrad_correction": 1,
-                                              "vert_remap_u_alg": 10})])
+                                              "vert_remap_u_alg": 10}),
+                                      # the full EAMxx set: tensor hyperviscosity hypervis_scaling = 3, nu = 3.4e-8, at L72 and L128
+                                      ("C2", dict(EAMXX := {"hypervis_scaling": 3.0, "nu": 3.4e-8, "nu_p": 3.4e-8, "nu_s": 3.4e-8,
+                                                            "nu_div": 3.4e-8, "hv_ref_profiles": 6, "theta_advect_form": 1,
+                                                            "pgrad_correction": 1, "vert_remap_u_alg": 10})),
+                                      ("C4", dict(EAMXX, nu_top=4.0e4, hypervis_subcycle_tom=1))])
 def test_steps_at_full_vertical_resolution(cfg, over):
     """The bench/scaling configurations at their real nlev (72 / 128 levels, their dt, hyperviscosity
     and sponge settings) on the coarse ne4 sphere: three steps from the JW state, GPU vs oracle."""
