@@ -69,6 +69,7 @@ struct Session {
   cudaEvent_t ev_pin[4]{}, ev_pdone[4]{}, ev_pd2h[4]{};
   long pipe_calls = 0; bool pipe_ready = false;
   int ftype = -1;           // forcing algorithm (control_mod.F90): 0 and 2 apply the pushed forcing per model step
+  double *d_ps_v[NTL] = {nullptr, nullptr, nullptr};   // elem%state%ps_v per time level, [ie][16]
   double *d_fm = nullptr, *d_fvtheta = nullptr, *d_fphi = nullptr;   // derived%FM (3 comps), FVTheta, FPHI
   bool have_forcing = false;
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
@@ -198,7 +199,17 @@ void finalize_hommexx_session(void)
   S.have_id = have_id; S.nccl_id = id;
 }
 
-void reset_cxx_comm(const int *f_comm) { (void)f_comm; }
+// mpi_cxx_f90_interface.cpp:20-23 converts the Fortran MPI communicator.  This library has no MPI: one rank
+// drives one GPU and the ranks meet through NCCL, whose rank/size/id come from thetal_b200_init_comm (the
+// Fortran shim passes par%rank, par%nprocs and the id rank 0 broadcasts over its own MPI_Bcast).  The handle is
+// kept only so that a second call with a different communicator is reported.
+void reset_cxx_comm(const int *f_comm)
+{
+  static int seen = -1;
+  if (seen != -1 && f_comm && *f_comm != seen && S.active)
+    fail(4, "reset_cxx_comm: communicator changed while a session is active; finalize_hommexx_session first");
+  if (f_comm) seen = *f_comm;
+}
 
 void thetal_b200_init_comm(const int *rank, const int *nranks, const int *device, const void *nccl_id)
 {
@@ -525,6 +536,7 @@ void init_functors_c(const int *allocate_buffer)
   S.ref.theta_ref = dalloc<double>((size_t)n * 16 * nlev);
   S.ref.dp_ref = dalloc<double>((size_t)n * 16 * nlev);
   S.ref.phi_ref = dalloc<double>((size_t)n * 16 * (nlev + 1));
+  for (int t = 0; t < NTL; t++) S.d_ps_v[t] = dalloc<double>((size_t)n * 16);
   S.d_err = dalloc<int>(1); S.d_maxiter = dalloc<int>(1); S.d_maxdelta = dalloc<unsigned long long>(1);
   S.d_diag_part = dalloc<double>((size_t)S.prm.nelem * NDIAG); S.d_diag_acc = dalloc<unsigned long long>(NDIAG + 2 + NDIAG * thetal_reprosum::NLIMB);
   if (S.nu_scale_top.empty()) S.nu_scale_top.assign(nlev, 0.0);
@@ -534,8 +546,20 @@ void init_functors_c(const int *allocate_buffer)
   S.device_ready = true;
 }
 
-void init_boundary_exchanges_c(void) {}
-void initialize_dp3d_from_ps_c(void) { fail(3, "initialize_dp3d_from_ps_c: pass dp3d through init_elements_states_c"); }
+// The exchange objects (gather table, per-peer halo lists and buffers) are created by finalize_connectivity and
+// init_functors_c; nothing is left to do here (theta_f2c_mod.F90:176-178 calls it after init_functors_c).
+void init_boundary_exchanges_c(void)
+{
+  REQUIRE(S.device_ready, "init_functors_c must precede init_boundary_exchanges_c");
+}
+// prim_driver.cpp:31-57: dp3d(n0) from ps_v(n0) on the reference levels
+void initialize_dp3d_from_ps_c(void)
+{
+  REQUIRE(S.device_ready && S.n0 >= 0 && S.n0 < NTL, "initialize_dp3d_from_ps_c before init_functors_c / init_time_level_c");
+  launch_dp_from_ps(S.tl[S.n0].dp, S.d_ps_v[S.n0], S.prm.nelem, S.nlev, S.prm.ps0, S.stream);
+  S.launches += 1;
+  thetal_b200_sync();
+}
 
 }  // extern "C"
 
@@ -784,7 +808,7 @@ extern "C" {
 void init_elements_states_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vtheta_dp,
     thetal_f90ptr phinh_i, thetal_f90ptr dp3d, thetal_f90ptr qdp, thetal_f90ptr ps_v)
 {
-  (void)qdp; (void)ps_v;
+  (void)qdp;
   REQUIRE(S.device_ready, "init_functors_c must precede init_elements_states_c");
   if (!S.device_ready) return;
   const size_t nlev = S.nlev;
@@ -795,6 +819,28 @@ void init_elements_states_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vt
   copy_state_h2d(*vtheta_dp, dth, 16 * nlev);
   copy_state_h2d(*phinh_i, dphi, 16 * (nlev + 1));
   copy_state_h2d(*dp3d, ddp, 16 * nlev);
+  if (ps_v && *ps_v) copy_state_h2d(*ps_v, S.d_ps_v, 16);          // ps_v(np,np,timelevels,nelemd)
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+}
+
+// Addition: the PLAIN theta-l build keeps the state inside an array of element structs
+// (element_mod.F90:32-144, elem(ie)%state%v(np,np,2,nlev,timelevels) ...).  base pointers = the field of
+// elem(1), elem_stride_bytes = storage size of one element_t: no Fortran-side copy into flat arrays.
+void init_elements_states_strided_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vtheta_dp,
+    thetal_f90ptr phinh_i, thetal_f90ptr dp3d, const long *elem_stride_bytes)
+{
+  REQUIRE(S.device_ready, "init_functors_c must precede init_elements_states_strided_c");
+  const size_t nlev = S.nlev, n = S.prm.nelem, stride = (size_t)*elem_stride_bytes;
+  REQUIRE(stride >= NTL * 32 * nlev * sizeof(double), "init_elements_states_strided_c: stride smaller than one element's v");
+  auto copy = [&](const double *h, int which, size_t per_elem) {
+    for (int t = 0; t < NTL; t++) {
+      double *d = which == 0 ? S.tl[t].v : which == 1 ? S.tl[t].w : which == 2 ? S.tl[t].th : which == 3 ? S.tl[t].phi : S.tl[t].dp;
+      CUDA_OK(cudaMemcpy2DAsync(d, per_elem * sizeof(double), h + t * per_elem, stride, per_elem * sizeof(double), n,
+                                cudaMemcpyHostToDevice, S.stream));
+    }
+  };
+  copy(*v, 0, 32 * nlev); copy(*w_i, 1, 16 * (nlev + 1)); copy(*vtheta_dp, 2, 16 * nlev);
+  copy(*phinh_i, 3, 16 * (nlev + 1)); copy(*dp3d, 4, 16 * nlev);
   CUDA_OK(cudaStreamSynchronize(S.stream));
 }
 
@@ -802,7 +848,7 @@ void cxx_push_results_to_f90(thetal_f90ptr_out v, thetal_f90ptr_out w_i, thetal_
     thetal_f90ptr_out phinh_i, thetal_f90ptr_out dp3d, thetal_f90ptr_out ps_v, thetal_f90ptr_out qdp,
     thetal_f90ptr_out q, thetal_f90ptr_out omega_p)
 {
-  (void)ps_v; (void)qdp; (void)q;
+  (void)qdp; (void)q;
   REQUIRE(S.device_ready, "no device state");
   if (!S.device_ready) return;
   const size_t nlev = S.nlev;
@@ -813,6 +859,11 @@ void cxx_push_results_to_f90(thetal_f90ptr_out v, thetal_f90ptr_out w_i, thetal_
   copy_state_d2h(*vtheta_dp, dth, 16 * nlev);
   copy_state_d2h(*phinh_i, dphi, 16 * (nlev + 1));
   copy_state_d2h(*dp3d, ddp, 16 * nlev);
+  if (ps_v && *ps_v) {         // ps_v = hyai(1) ps0 + sum dp3d of every time level (vertremap_mod.F90:79-84)
+    for (int t = 0; t < NTL; t++) launch_ps_from_dp(S.tl[t].dp, S.d_ps_v[t], S.prm.nelem, S.nlev, S.prm.ptop, S.stream);
+    S.launches += NTL;
+    copy_state_d2h(*ps_v, S.d_ps_v, 16);
+  }
   if (omega_p && *omega_p)
     CUDA_OK(cudaMemcpyAsync(*omega_p, S.der.omega_p, (size_t)S.prm.nelem * 16 * nlev * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
   CUDA_OK(cudaStreamSynchronize(S.stream));

@@ -1526,6 +1526,35 @@ void launch_forcing(const StatePtrs &s, const double *fm, const double *fvtheta,
   forcing_kernel<<<nelem, 256, 0, st>>>(s, fm, fvtheta, fphi, geo, dt, nlev);
 }
 
+// ps_v = hyai(1) ps0 + sum_k dp3d (vertremap_mod.F90:79-84) and its inverse on the reference levels,
+// dp3d(k) = (hyai(k+1)-hyai(k)) ps0 + (hybi(k+1)-hybi(k)) ps_v (prim_driver.cpp:31-57); one thread per column
+__global__ void ps_from_dp_kernel(const double *dp, double *ps, int nelem, int nlev, double ptop)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nelem * 16) return;
+  const int ie = i >> 4, p = i & 15;
+  double s = ptop;
+  for (int k = 0; k < nlev; k++) s = s + dp[(size_t)ie * 16 * nlev + k * 16 + p];
+  ps[i] = s;
+}
+__global__ void dp_from_ps_kernel(double *dp, const double *ps, int nelem, int nlev, double ps0)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nelem * 16) return;
+  const int ie = i >> 4, p = i & 15;
+  const double psv = ps[i];
+  for (int k = 0; k < nlev; k++)
+    dp[(size_t)ie * 16 * nlev + k * 16 + p] = (c_hyai[k + 1] - c_hyai[k]) * ps0 + (c_hybi[k + 1] - c_hybi[k]) * psv;
+}
+void launch_ps_from_dp(const double *dp, double *ps, int nelem, int nlev, double ptop, cudaStream_t st)
+{
+  ps_from_dp_kernel<<<(nelem * 16 + 255) / 256, 256, 0, st>>>(dp, ps, nelem, nlev, ptop);
+}
+void launch_dp_from_ps(double *dp, const double *ps, int nelem, int nlev, double ps0, cudaStream_t st)
+{
+  dp_from_ps_kernel<<<(nelem * 16 + 255) / 256, 256, 0, st>>>(dp, ps, nelem, nlev, ps0);
+}
+
 // FP64 FMA peak probe: 8 independent DFMA chains per thread, 1024 threads per CTA, 2 CTAs per SM
 __global__ void __launch_bounds__(1024) fp64_peak_kernel(double *sink, int n)
 {

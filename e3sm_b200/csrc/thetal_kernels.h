@@ -90,6 +90,8 @@ void upload_hyai(const double *hyai, int nlev);
 void launch_vertical_remap(const RemapArgs &A, cudaStream_t st);
 void launch_forcing(const StatePtrs &s, const double *fm, const double *fvtheta, const double *fphi, const Geo &geo,
                     double dt, int nelem, int nlev, cudaStream_t st);
+void launch_ps_from_dp(const double *dp, double *ps, int nelem, int nlev, double ptop, cudaStream_t st);
+void launch_dp_from_ps(double *dp, const double *ps, int nelem, int nlev, double ps0, cudaStream_t st);
 double launch_fp64_peak(cudaStream_t st);   // returns the flops the launch performs
 void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st);
 

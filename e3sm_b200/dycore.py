@@ -153,18 +153,29 @@ class ThetaLDycore:
             self.L.thetal_b200_clear_error()
             raise RuntimeError("libthetal_b200: " + msg)
 
-    def set_state(self, st):
-        """init_elements_states_c: host (flat Fortran layout) -> device."""
+    def set_state(self, st, ps_v=None):
+        """init_elements_states_c: host (flat Fortran layout) -> device; ps_v [ie][tl][16] optional."""
         self.L.init_elements_states_c(_pp(st.v), _pp(st.w_i), _pp(st.vtheta_dp), _pp(st.phinh_i),
-                                      _pp(st.dp3d), None, None)
+                                      _pp(st.dp3d), None, None if ps_v is None else _pp(ps_v))
         self._check()
 
-    def get_state(self, st=None):
-        """cxx_push_results_to_f90: device -> host."""
+    def set_state_strided(self, v, w_i, vtheta_dp, phinh_i, dp3d, stride_bytes):
+        """init_elements_states_strided_c: the fields of elem(1) inside an array of element structs."""
+        pp = lambda a: byref(c_void_p(a))
+        self.L.init_elements_states_strided_c(pp(v), pp(w_i), pp(vtheta_dp), pp(phinh_i), pp(dp3d),
+                                              byref(ctypes.c_long(int(stride_bytes))))
+        self._check()
+
+    def initialize_dp3d_from_ps(self):
+        self.L.initialize_dp3d_from_ps_c()
+        self._check()
+
+    def get_state(self, st=None, ps_v=None):
+        """cxx_push_results_to_f90: device -> host (ps_v [ie][tl][16] is filled when given)."""
         if st is None:
             st = State(self.nelem, self.nlev)
         self.L.cxx_push_results_to_f90(_pp(st.v), _pp(st.w_i), _pp(st.vtheta_dp), _pp(st.phinh_i),
-                                       _pp(st.dp3d), None, None, None, None)
+                                       _pp(st.dp3d), None if ps_v is None else _pp(ps_v), None, None, None)
         self._check()
         return st
 

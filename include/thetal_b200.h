@@ -77,7 +77,11 @@ void init_reference_states_c(thetal_f90ptr theta_ref, thetal_f90ptr dp_ref, thet
     thetal_f90ptr nu_scale_top);
 void init_functors_c(const int *allocate_buffer);
 void init_boundary_exchanges_c(void);
-void initialize_dp3d_from_ps_c(void);
+void initialize_dp3d_from_ps_c(void);   /* dp3d(n0) = dA ps0 + dB ps_v(n0), prim_driver.cpp:31-57 */
+/* addition: state embedded in the plain theta-l array of element structs (element_mod.F90:32-144):
+ * base pointers of elem(1)%state%..., stride = storage size of element_t in bytes */
+void init_elements_states_strided_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f90ptr vtheta_dp,
+    thetal_f90ptr phinh_i, thetal_f90ptr dp3d, const long *elem_stride_bytes);
 
 /* ---- run time: theta_f2c_mod.F90:189-236; impl H/src/share/cxx/prim_driver.cpp:60-181 */
 /* derived%FM(np,np,3,nlev,nelemd), FVTheta(np,np,nlev,nelemd), FT (unused), FPHI(np,np,nlevp,nelemd), FQ (qsize = 0:

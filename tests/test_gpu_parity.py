@@ -556,3 +556,54 @@ def test_forcing_through_prim_run_subcycle(case_c1, parity_state_c1):
     d.apply_forcing_dynamics(n0, 123.0)
     assert_state_close(d.get_state(), so, n0, 1e-9, "applyCAMforcing_dynamics")
     d.close()
+
+
+# ---------------------------------------------------------------- boundary (b): the smaller entry points
+def test_state_inside_array_of_element_structs(case_c1, parity_state_c1):
+    """init_elements_states_strided_c: the plain theta-l build keeps elem(ie)%state inside element_t
+    (element_mod.F90:32-144); base pointers of elem(1) + the struct size reach the same device state"""
+    from e3sm_b200.dycore import ThetaLDycore
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    st = distinct_levels(parity_state_c1, phis, gradphis)
+    n, nlev = grid.nelem, hv.nlev
+    sizes = {"v": 3 * nlev * 32, "w_i": 3 * (nlev + 1) * 16, "vtheta_dp": 3 * nlev * 16,
+             "phinh_i": 3 * (nlev + 1) * 16, "dp3d": 3 * nlev * 16}
+    pad = 37                                     # other members of element_t between and after the state fields
+    rec = sum(sizes.values()) + pad * (len(sizes) + 1)
+    buf = np.full((n, rec), np.nan)
+    off, o = {}, pad
+    for f, sz in sizes.items():
+        off[f] = o
+        buf[:, o:o + sz] = getattr(st, f).reshape(n, sz)
+        o += sz + pad
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+    base = buf.ctypes.data
+    d.set_state_strided(*[base + 8 * off[f] for f in ("v", "w_i", "vtheta_dp", "phinh_i", "dp3d")], rec * 8)
+    out = d.get_state()
+    for f in sizes:
+        assert np.array_equal(getattr(out, f), getattr(st, f)), f
+    d.close()
+
+
+def test_ps_v_and_initialize_dp3d_from_ps(case_c1, parity_state_c1):
+    """initialize_dp3d_from_ps_c (prim_driver.cpp:31-57) and the ps_v that cxx_push_results_to_f90 returns
+    (hyai(1) ps0 + sum dp3d, vertremap_mod.F90:79-84)"""
+    from e3sm_b200.dycore import ThetaLDycore
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    st = parity_state_c1.copy()
+    n, nlev = grid.nelem, hv.nlev
+    rng = np.random.default_rng(3)
+    ps = np.ascontiguousarray(hv.ps0 * (1 + 0.02 * rng.uniform(-1, 1, (n, 3, 16))))
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+    d.set_state(st, ps_v=ps)
+    d.init_time_level(1, 2, 3)
+    d.initialize_dp3d_from_ps()
+    back = np.zeros_like(ps)
+    out = d.get_state(ps_v=back)
+    dA, dB = np.diff(hv.hyai), np.diff(hv.hybi)
+    want = dA[None, :, None] * hv.ps0 + dB[None, :, None] * ps[:, 1][:, None, :]
+    assert rel_l2(out.dp3d[:, 1], want) <= 1e-15
+    assert np.array_equal(out.dp3d[:, 0], st.dp3d[:, 0])                 # only time level n0 is touched
+    assert rel_l2(back[:, 1], ps[:, 1]) <= 1e-14                          # sum of the new layers = ps_v again
+    assert rel_l2(back[:, 0], hv.hyai[0] * hv.ps0 + st.dp3d[:, 0].sum(axis=1)) <= 1e-15
+    d.close()
