@@ -336,6 +336,22 @@ def run_ours(args, world, rank, local, td):
                 "by_family": {k: {"launch_ms": fam_ms[k] / nl[k], "GBps": nelem * alg[k] / (fam_ms[k] / nl[k] * 1e-3) / 1e9,
                                   "frac": nelem * alg[k] / (fam_ms[k] / nl[k] * 1e-3) / 1e9 / peak} for k in nl}}
     step_gbs = nelem_total * bstep / (ms / K * 1e-3) / 1e9
+    if args.no_e2e:      # capacity runs (C4: 14.5 GB of state per rank): device-resident numbers only
+        n_exch, halo_bytes = d.halo_stats()
+        d.close()
+        if rank == 0:
+            emit({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                  "ms_per_step": ms / K, "higher_is_better": True,
+                  "scaling": "weak" if (world == 1 or args.weak_ne) else "strong", "vs_baseline": None,
+                  "dtype": "f64", "data": "synthetic",
+                  "config": {"workload": workload_string(args.config, p, nelem_total, args.weak_ne),
+                             "parallelism": f"1 rank per GPU, {world} ranks, {nelem} elements on rank 0, "
+                                            f"{halo_bytes / max(n_exch, 1) / 1e6:.2f} MB per exchange on rank 0"},
+                  "sypd": p.tstep * (value / nelem_total) / 365.0, "hbm_gbs_step": step_gbs,
+                  "hbm_frac_step": step_gbs / (peak * world), "alg_bytes_per_element_step": bstep,
+                  "state_GB_per_gpu": nelem * 3 * S / 1e9, "kernel_ms_per_step": fam_ms, "roofline": roofline,
+                  "answer_check": answer, "e2e": None, "gpu_launches": launches, "clocks": clocks})
+        return
     # ---- end to end through the reference's own call triple, Fortran-layout host arrays ----
     # init_elements_states_c (H2D, all three time levels) -> prim_run_subcycle_c (rsplit*qsplit dynamics
     # steps + vertical remap, what the Fortran driver calls per model step) -> cxx_push_results_to_f90 (D2H)
@@ -490,6 +506,7 @@ def main():
                          "curve) as `value`, plus a `strong` block: C3 (ne120np4 L72) on the N GPUs and on one GPU; "
                          "pass --config C3 to make the ne120 strong-scaling case the line's own value")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="device-resident timing only (capacity runs such as C4)")
     ap.add_argument("--no-strong", dest="strong", action="store_false",
                     help="skip the C3 strong-scaling block of the default N>1 run")
     args = ap.parse_args()

@@ -74,7 +74,7 @@ struct Session {
   bool have_forcing = false;
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
   int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
-  int overlap = 0;          // measured on 2 and 8 B200: the split launches cost more than the hidden exchange saves
+  int overlap = 1;          // halo of a DSS travels while the producer runs on the interior elements
   // device
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -163,10 +163,12 @@ void initialize_hommexx_session(void)
   CUDA_OK(cudaEventCreate(&S.ev0));
   CUDA_OK(cudaEventCreate(&S.ev1));
   if (S.nranks > 1) {
-    CUDA_OK(cudaStreamCreateWithFlags(&S.stream2, cudaStreamNonBlocking));
+    int prio_lo = 0, prio_hi = 0;
+    CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CUDA_OK(cudaStreamCreateWithPriority(&S.stream2, cudaStreamNonBlocking, prio_hi));   // halo stream: its CTAs go first
     CUDA_OK(cudaEventCreateWithFlags(&S.ev_prod, cudaEventDisableTiming));
     CUDA_OK(cudaEventCreateWithFlags(&S.ev_halo, cudaEventDisableTiming));
-    if (getenv("THETAL_B200_OVERLAP")) S.overlap = 1;         // A/B switch (off by default)
+    if (getenv("THETAL_B200_OVERLAP")) S.overlap = atoi(getenv("THETAL_B200_OVERLAP"));   // A/B switch, default 1
     if (!S.have_id) { fail(4, "nranks > 1 needs the ncclUniqueId of rank 0 (thetal_b200_init_comm)"); return; }
     ncclResult_t r = ncclCommInitRank(&S.comm, S.nranks, S.nccl_id, S.rank);
     if (r != ncclSuccess) { fail(5, std::string("ncclCommInitRank: ") + ncclGetErrorString(r)); return; }
@@ -636,20 +638,26 @@ void halo_exchange(const StatePtrs &t, int nk, int wbot, cudaStream_t st)
   S.halo_bytes += (long)(S.hsend_idx.size() + S.hrecv_idx.size()) * nlyr * 8;
 }
 
-// One DSS across ranks: `consume(elist, count)` launches the kernel that gathers from `t` (on S.stream)
-// for the listed elements (null = all).  The halo of `t` travels on stream2 while the elements with
-// no ghost neighbour are consumed; the partition-boundary elements follow once it has been unpacked.
-template <class F> void exchange_and_consume(const StatePtrs &t, int nk, int wbot, F consume)
+// One DSS across ranks.  `produce(elist, count)` launches, on the stream it is given, the kernel that writes
+// the pre-DSS buffer `t` for the listed elements (null = all).  The partition-boundary elements are produced
+// first, on the high-priority halo stream, followed there by the pack and the ncclSend/ncclRecv group; the
+// interior elements are produced meanwhile on the main stream, which then waits for the halo.  The kernel
+// that gathers from `t` is launched by the caller on the main stream for all elements.  (Reading the
+// contributions of other ranks straight from the receive buffer instead of ghost slots was measured and
+// dropped: the second address form in dss_sum stops the compiler from batching the neighbour loads and
+// doubles the time of every gather kernel, 0.80 -> 1.75 ms per step for the five DSS/post launches.)
+template <class F> void produce_and_exchange(const StatePtrs &t, int nk, int wbot, F produce)
 {
-  if (S.peers.empty()) { consume(nullptr, 0); return; }
-  if (!S.overlap) { halo_exchange(t, nk, wbot, S.stream); consume(nullptr, 0); return; }
+  if (S.peers.empty()) { produce(nullptr, 0, S.stream); return; }
+  if (!S.overlap) { produce(nullptr, 0, S.stream); halo_exchange(t, nk, wbot, S.stream); return; }
   CUDA_OK(cudaEventRecord(S.ev_prod, S.stream));
   CUDA_OK(cudaStreamWaitEvent(S.stream2, S.ev_prod, 0));
+  produce(S.d_boundary, (int)S.h_boundary.size(), S.stream2);
   halo_exchange(t, nk, wbot, S.stream2);
   CUDA_OK(cudaEventRecord(S.ev_halo, S.stream2));
-  consume(S.d_interior, (int)S.h_interior.size());
+  produce(S.d_interior, (int)S.h_interior.size(), S.stream);
   CUDA_OK(cudaStreamWaitEvent(S.stream, S.ev_halo, 0));
-  consume(S.d_boundary, (int)S.h_boundary.size());
+  S.launches += 1;
 }
 
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
@@ -659,17 +667,18 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
   CaarArgs a;
   a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
   a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
-  { ProfScope ps(0); launch_caar_pre(a, S.stream); }
+  {
+    ProfScope ps(0);
+    Nvtx rx("caar_bexchV");
+    produce_and_exchange(S.tensA, S.nlev, 1, [&](const int *el, int n, cudaStream_t st) {
+      a.elist = el; a.ecount = n; launch_caar_pre(a, st); });
+  }
   DssArgs d;
   d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
   d.do_limiter = (s3 != 0.0);
-  {
-    ProfScope ps(1);
-    Nvtx rx("caar_bexchV");
-    exchange_and_consume(S.tensA, S.nlev, 1, [&](const int *el, int n) {
-      d.elist = el; d.ecount = n; launch_caar_dss_post(d, S.stream); S.launches += 1; });
-  }
-  S.launches += 1;
+  d.elist = nullptr; d.ecount = 0;
+  { ProfScope ps(1); launch_caar_dss_post(d, S.stream); }
+  S.launches += 2;
 }
 
 void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
@@ -696,15 +705,15 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
   for (int ic = 0; ic < hvs; ic++) {
     a.dt = dt2 / hvs;
     a.th_is_theta = ic > 0; a.last_subcycle = (ic == hvs - 1);
-    a.elist = nullptr; a.ecount = 0;
-    a.nu_ratio = nu_ratio1; a.tin = S.tensB; a.tout = S.tensA; launch_hv(0, a, S.stream);
-    a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB;
+    a.nu_ratio = nu_ratio1; a.tin = S.tensB; a.tout = S.tensA;
     { Nvtx rx("biwkdp3d_bexchV");
-      exchange_and_consume(S.tensA, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(1, a, S.stream); }); }
-    a.tin = S.tensB; a.tout = S.tensA;
+      produce_and_exchange(S.tensA, S.nlev, 0, [&](const int *el, int n, cudaStream_t st) { a.elist = el; a.ecount = n; launch_hv(0, a, st); }); }
+    a.nu_ratio = 1.0;       a.tin = S.tensA; a.tout = S.tensB;
     { Nvtx rx("ahdp_bexchV2");
-      exchange_and_consume(S.tensB, S.nlev, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(2, a, S.stream); }); }
+      produce_and_exchange(S.tensB, S.nlev, 0, [&](const int *el, int n, cudaStream_t st) { a.elist = el; a.ecount = n; launch_hv(1, a, st); }); }
+    a.tin = S.tensB; a.tout = S.tensA;
     a.elist = nullptr; a.ecount = 0;
+    launch_hv(2, a, S.stream);
     S.launches += 3;
   }
   if (hvs == 0) fail(3, "hypervis_subcycle must be >= 1");
@@ -712,11 +721,11 @@ void run_hypervis(int nt, double dt2, double eta_ave_w)
     const int nt_ = S.prm.hypervis_subcycle_tom;
     for (int ic = 0; ic < nt_; ic++) {
       a.dt = dt2 / nt_; a.th_is_theta = 0; a.last_subcycle = 0;
-      a.elist = nullptr; a.ecount = 0;
-      a.tin = S.tensB; a.tout = S.tensA; launch_hv(3, a, S.stream);
+      a.tin = S.tensB; a.tout = S.tensA;
+      produce_and_exchange(S.tensA, S.prm.nlev_tom, 0, [&](const int *el, int n, cudaStream_t st) { a.elist = el; a.ecount = n; launch_hv(3, a, st); });
       a.tin = S.tensA; a.tout = S.tensB;
-      exchange_and_consume(S.tensA, S.prm.nlev_tom, 0, [&](const int *el, int n) { a.elist = el; a.ecount = n; launch_hv(4, a, S.stream); });
       a.elist = nullptr; a.ecount = 0;
+      launch_hv(4, a, S.stream);
       S.launches += 2;
     }
   }

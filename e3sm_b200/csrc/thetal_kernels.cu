@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
-  const int ie = blockIdx.x, tid = threadIdx.x;
+  const int ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   double *sv = smem;                       // [k][2][16]
   double *sdp = sv + 32 * nlev;            // [k][16]
   double *sth = sdp + 16 * nlev;
@@ -455,7 +455,8 @@ static void launch_caar_pre_t(const CaarArgs &A, cudaStream_t st)
     cudaFuncSetAttribute(caar_pre_kernel<FORM, PGRAD, ACCUM, VADV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     configured = sm;
   }
-  caar_pre_kernel<FORM, PGRAD, ACCUM, VADV><<<A.prm.nelem, CAAR_THREADS, sm, st>>>(A);
+  const int nb = A.elist ? A.ecount : A.prm.nelem;
+  if (nb > 0) caar_pre_kernel<FORM, PGRAD, ACCUM, VADV><<<nb, CAAR_THREADS, sm, st>>>(A);
 }
 
 template <int FORM, bool PGRAD>
@@ -1203,7 +1204,7 @@ __host__ __device__ inline size_t hv_smem_bytes() { return sizeof(double) * (HV_
 __global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace1_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
   double *scr = smem + kslot * (HV_SLOTS * 16);
@@ -1367,7 +1368,7 @@ __global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A
 __global__ void __launch_bounds__(HV_THREADS, 2) hv_sponge_laplace_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
   double *scr = smem + kslot * (HV_SLOTS * 16);
@@ -1419,16 +1420,16 @@ __global__ void __launch_bounds__(HV_THREADS) hv_sponge_update_kernel(const HvAr
 void launch_hv(int which, const HvArgs &A, cudaStream_t st)
 {
   const size_t sm = hv_smem_bytes();
-  const int nb = A.elist ? A.ecount : A.prm.nelem;     // element lists only for the DSS consumers 1, 2, 4
+  const int nb = A.elist ? A.ecount : A.prm.nelem;
   if (nb <= 0) return;
   switch (which) {
-    case 0: hv_laplace1_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
+    case 0: hv_laplace1_kernel<<<nb, HV_THREADS, sm, st>>>(A); break;
     case 1:
       if (A.prm.hypervis_scaling_on) hv_laplace2_kernel<true><<<nb, HV_THREADS, sm, st>>>(A);
       else hv_laplace2_kernel<false><<<nb, HV_THREADS, sm, st>>>(A);
       break;
     case 2: hv_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
-    case 3: hv_sponge_laplace_kernel<<<A.prm.nelem, HV_THREADS, sm, st>>>(A); break;
+    case 3: hv_sponge_laplace_kernel<<<nb, HV_THREADS, sm, st>>>(A); break;
     case 4: hv_sponge_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
   }
 }
@@ -1643,12 +1644,6 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(StatePtrs t, const int
   *halo_addr(t, idx[ent], layer, nk, nlev) = buf[i];
 }
 
-void launch_halo_pack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev, double *buf,
-                      cudaStream_t st)
-{
-  const long n = (long)nent * (6 * nk + wbot);
-  if (n > 0) halo_pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, idx, nent, nk, wbot, nlev, buf);
-}
 void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev,
                         const double *buf, cudaStream_t st)
 {
@@ -1656,6 +1651,12 @@ void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, in
   if (n > 0) halo_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, idx, nent, nk, wbot, nlev, buf);
 }
 
+void launch_halo_pack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev, double *buf,
+                      cudaStream_t st)
+{
+  const long n = (long)nent * (6 * nk + wbot);
+  if (n > 0) halo_pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, idx, nent, nk, wbot, nlev, buf);
+}
 // ---------------------------------------------------------------- global diagnostics
 // prim_energy_halftimes (prim_state_mod.F90:822-939) per element, then global_integral
 // (global_norms_mod.F90:47-90): J(ie) = sum_{j,i} spheremp * h in the reference's point order, and

@@ -6,6 +6,8 @@
 namespace thetal {
 
 struct CaarArgs {
+  const int *elist = nullptr;   // optional element list (partition-boundary / interior pass); null = all
+  int ecount = 0;
   StatePtrs n0, nm1, tens;
   Geo geo;
   Derived der;
@@ -20,7 +22,7 @@ struct DssArgs {
   Params prm;
   double dt2, scale1, scale3;
   int do_limiter;
-  const int *elist;         // optional element list (interior / partition-boundary pass); null = all
+  const int *elist;         // optional element list; null = all
   int ecount;
 };
 
@@ -43,7 +45,7 @@ struct HvArgs {
   double dt, nu_ratio;
   int th_is_theta;          // st.th currently holds theta (not vtheta_dp)
   int last_subcycle;        // convert back to vtheta_dp and reset w b.c. (PA:767-774)
-  const int *elist;         // optional element list for the DSS-consuming kernels; null = all
+  const int *elist;         // optional element list (partition-boundary / interior pass); null = all
   int ecount;
 };
 
