@@ -173,7 +173,8 @@ def workload_string(name, p, nelem_total, weak_ne=0):
     return (f"{name}{' (weak scaling: ne = 30*sqrt(N), ~5400 elements per GPU)' if weak_ne else ''}"
             f": theta-l NH JW baroclinic wave ne{p.ne}np4 L{p.nlev}, {nelem_total} elements"
             f", tstep_type {p.tstep_type}, dt={p.tstep:g}s, hypervis_subcycle {p.hypervis_subcycle}, "
-            f"nu={p.nu:g}, nu_div={p.nu_div:g}, nu_top={p.nu_top:g}, sponge on{dev}")
+            f"nu={p.nu:g}, nu_div={p.nu_div:g}, nu_top={p.nu_top:g}, "
+            f"sponge {'on' if (p.nu_top > 0 and p.hypervis_subcycle_tom > 0) else 'off'}{dev}")
 
 
 def run_reference(args, world, rank, td):

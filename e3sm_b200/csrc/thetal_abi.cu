@@ -74,6 +74,7 @@ struct Session {
   bool have_forcing = false;
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
   int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
+  int expl_cache = 1;       // THETAL_B200_EXPL_CACHE=0: the closing DIRK stage redoes the EOS of state(n0), state(nm1)
   int overlap = 1;          // halo of a DSS travels while the producer runs on the interior elements
   // device
   cudaStream_t stream = nullptr;
@@ -160,6 +161,7 @@ void initialize_hommexx_session(void)
   if (e != cudaSuccess || ndev == 0) { fail(1, "no CUDA device: libthetal_b200 has no CPU fallback"); return; }
   CUDA_OK(cudaSetDevice(S.device % ndev));
   CUDA_OK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
+  if (getenv("THETAL_B200_EXPL_CACHE")) S.expl_cache = atoi(getenv("THETAL_B200_EXPL_CACHE"));
   CUDA_OK(cudaEventCreate(&S.ev0));
   CUDA_OK(cudaEventCreate(&S.ev1));
   if (S.nranks > 1) {
@@ -661,10 +663,14 @@ template <class F> void produce_and_exchange(const StatePtrs &t, int nk, int wbo
 }
 
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
-void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3)
+// save_expl: 0 = no, 1 / 2 = keep the explicit stiff terms of state(n0) for the closing DIRK stage of this step in the
+// (otherwise idle) hyperviscosity scratch tensB: w/phi slots (1) or dp/th slots (2)
+void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3, int save_expl = 0)
 {
   Nvtx r("compute_andor_apply_rhs");
   CaarArgs a;
+  if (save_expl == 1) { a.ew = S.tensB.w; a.ephi = S.tensB.phi; }
+  if (save_expl == 2) { a.ew = S.tensB.dp; a.ephi = S.tensB.th; }
   a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.tens = S.tensA; a.geo = S.geo; a.der = S.der; a.prm = S.prm;
   a.dt2 = dt2; a.eta_ave_w = eta_ave_w; a.scale1 = s1; a.scale2 = s2; a.scale3 = s3; a.err = S.d_err;
   {
@@ -681,10 +687,12 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
   S.launches += 2;
 }
 
-void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2)
+// cached: the explicit terms of state(n0) were saved by run_caar(..., save_expl = 1), those of state(nm1) by save_expl = 2
+void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2, bool cached = false)
 {
   Nvtx r("compute_stage_value_dirk");
   DirkArgs a;
+  if (cached && S.expl_cache && S.prm.rsplit > 0) { a.ew_n0 = S.tensB.w; a.ephi_n0 = S.tensB.phi; a.ew_nm1 = S.tensB.dp; a.ephi_nm1 = S.tensB.th; }
   a.np1 = S.tl[np1]; a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.geo = S.geo; a.prm = S.prm;
   a.dt2 = dt2; a.alphadt_n0 = a_n0; a.alphadt_nm1 = a_nm1;
   a.err = S.d_err; a.max_iter = S.d_maxiter; a.max_deltaerr_bits = S.d_maxdelta;
@@ -780,28 +788,28 @@ void run_prim_advance_exp(double dt, int nm1, int n0, int np1)
       break;
     }
     case 9: {
-      run_caar(nm1, n0, n0, dt / 5, eta_ave_w / 4, 1, 0, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt / 5);
-      run_caar(np1, n0, nm1, dt / 5, 0.0, 1, 0, 1);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 5);
+      run_caar(nm1, n0, n0, dt / 5, eta_ave_w / 4, 1, 0, 1, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt / 5);
+      run_caar(np1, n0, nm1, dt / 5, 0.0, 1, 0, 1, 2);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 5);
       run_caar(np1, n0, np1, dt / 3, 0.0, 1, 0, 1);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 3);
       run_caar(np1, n0, np1, 2 * dt / 3, 0.0, 1, 0, 1);       run_dirk(nm1, 0.0, n0, 0.0, np1, 2 * dt / 3);
       run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1);
       run_combo(9, np1, nm1, n0);
       const double a1 = 5 * dt / 18, a2 = dt / 36, a3 = 8 * dt / 18;
-      run_dirk(nm1, a2, n0, a1, np1, a3);
+      run_dirk(nm1, a2, n0, a1, np1, a3, true);     // neither state(n0) nor state(nm1) changed since stages 1 and 2
       break;
     }
     case 10: {
       double dt2 = dt / 4;
-      run_caar(nm1, n0, n0, dt2, 0.0, 1, 0, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt2);
+      run_caar(nm1, n0, n0, dt2, 0.0, 1, 0, 1, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt2);
       dt2 = dt / 6;
-      run_caar(np1, n0, nm1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      run_caar(np1, n0, nm1, dt2, 0.0, 1, 0, 1, 2); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
       dt2 = 3 * dt / 8;
       run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
       dt2 = dt / 2;
       run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
       run_caar(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 0, 1);
       const double a1 = .24362, a2 = .34184, a3 = 1 - (a1 + a2);
-      run_dirk(nm1, a2 * dt, n0, a1 * dt, np1, a3 * dt);
+      run_dirk(nm1, a2 * dt, n0, a1 * dt, np1, a3 * dt, true);
       break;
     }
     default: fail(3, "bad choice of tstep_type");

@@ -150,7 +150,12 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     cp_async_commit();
   };
   auto prefetch_explicit = [&](int e) {
-    if (tid < 10) {
+    if (A.ew_n0 && A.ew_nm1) {
+      if (tid < 4 && (A.alphadt_n0 != 0.0 || A.alphadt_nm1 != 0.0)) {
+        const double *f = tid == 0 ? A.ew_n0 : tid == 1 ? A.ephi_n0 : tid == 2 ? A.ew_nm1 : A.ephi_nm1;
+        prefetch_l2(f + (size_t)e * n16, 16u * nlev * 8u);
+      }
+    } else if (tid < 10) {
       const StatePtrs &S = tid < 5 ? A.n0 : A.nm1;
       const bool on = tid < 5 ? A.alphadt_n0 != 0.0 : A.alphadt_nm1 != 0.0;
       const int f = tid % 5;
@@ -210,8 +215,29 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   for (int i = 1; i < NW; i++) wmax = fmax(wmax, red[2][i]);
   wmax = fmax(1.0, wmax);
 
-  // ---- explicit stiff terms of earlier stages (IM:176-205): the n0 / nm1 columns of this element pass
-  // through the staging area (every thread has read its np1 slice before the barrier above) ----
+  // ---- explicit stiff terms of earlier stages (IM:176-205) ----
+  const bool expl = A.alphadt_n0 != 0.0 || A.alphadt_nm1 != 0.0;
+  if (expl && A.ew_n0 && A.ew_nm1) {
+    // saved by the CAAR launches that evaluated state(n0) and state(nm1) (dpnh_dp_i - 1 and g w - gwphis): four
+    // interface fields pass through the staging area (every thread has read its np1 slice before the barrier above)
+    const double *e0 = A.ew_n0 + (size_t)ie * n16, *p0 = A.ephi_n0 + (size_t)ie * n16;
+    const double *e1 = A.ew_nm1 + (size_t)ie * n16, *p1 = A.ephi_nm1 + (size_t)ie * n16;
+    for (int q = tid; q < n16; q += NT) {
+      const int o = (q & 15) * SS + (q >> 4);
+      cp_async8(st_th + o, e0 + q); cp_async8(st_dp + o, p0 + q);
+      cp_async8(st_w + o, e1 + q);  cp_async8(st_phi + o, p1 + q);
+    }
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const int kk = min(k0 + i, nlev - 1);
+      if (A.alphadt_n0 != 0.0) { w0[i] = w0[i] + A.alphadt_n0 * g * cth[kk]; phi0[i] = phi0[i] + A.alphadt_n0 * cdp[kk]; }
+      if (A.alphadt_nm1 != 0.0) { w0[i] = w0[i] + A.alphadt_nm1 * g * cw[kk]; phi0[i] = phi0[i] + A.alphadt_nm1 * cphi[kk]; }
+    }
+  } else
+  // from the states themselves: the n0 / nm1 columns of this element pass through the staging area
   for (int pass = 0; pass < 2; pass++) {
     const double dt3 = pass == 0 ? A.alphadt_n0 : A.alphadt_nm1;
     if (dt3 == 0.0) continue;
@@ -242,7 +268,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   }
   // the staging area is consumed: fetch the next element of this CTA behind the Newton iterations
   if (ie_next < nelem) {
-    if (A.alphadt_n0 != 0.0 || A.alphadt_nm1 != 0.0) __syncthreads();
+    if (expl) __syncthreads();
     stage_state(A.np1, ie_next);
   }
   // ---- wphis(np1) term (IM:208-211) ----

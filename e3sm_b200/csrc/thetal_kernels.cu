@@ -170,7 +170,8 @@ __host__ __device__ inline size_t caar_smem_bytes(int nlev, bool vadv)
 // FORM = theta_advect_form, PGRAD = pgrad_correction, ACCUM = (eta_ave_w != 0), VADV = (rsplit == 0, the
 // vertically Eulerian terms of PA:1227-1303 and prim_si_mod.F90:94-148): compile-time so that the level
 // loop is one straight-line block the scheduler can interleave freely
-template <int FORM, bool PGRAD, bool ACCUM, bool VADV>
+// SAVE = also store the explicit stiff terms of state(n0) for the closing DIRK stage (IM:176-205)
+template <int FORM, bool PGRAD, bool ACCUM, bool VADV, bool SAVE>
 __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArgs A)
 {
   extern __shared__ double smem[];
@@ -369,6 +370,10 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     const double v_gradphi = v1i_k * gphi1_k + v2i_k * gphi2_k;
     double phi_tens = (-phi_vadv_k - v_gradphi) * s1 + s2 * G_GRAV * wk;
     if (s1 != s2) phi_tens = phi_tens + (s1 - s2) * (v1i_k * gps1 + v2i_k * gps2) * c_hybi[k];
+    if (SAVE && act) {          // IM:176-205 for a later DIRK stage: dpnh_dp_i - 1 and g w - gwphis (IM:42-53) of this state
+      A.ew[gq] = mu_k - 1;
+      A.ephi[gq] = G_GRAV * wk - (k == 0 ? 0.0 : (v1i_k * gps1 + v2i_k * gps2) * c_hybi[k]);
+    }
 
     // momentum PA:1404-1509
     wv1 = wv1 - (wk * gw1_k + wk1 * gw1_k1) / 2;
@@ -404,11 +409,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       A.tens.w[gqi] = spheremp * (s3 * m_w + dt2 * w_tens);
       A.tens.phi[gqi] = spheremp * (s3 * m_phi + dt2 * phi_tens);
       A.tens.dp[gq] = spheremp * (s3 * m_dp - s1 * dt2 * (VADV ? divdp + deta : divdp));   // PA:1693-1694
-      if (accum) {
-        sdiv[q] = divdp;
-        A.der.vn0[gqv] += A.eta_ave_w * (v1 * dp);                                  // PA:1190
-        A.der.vn0[gqv + 16] += A.eta_ave_w * (v2 * dp);
-      }
+      if (accum) sdiv[q] = divdp;          // derived%vn0, omega_p are accumulated after the loop (phase 3/4)
       if (k == nlev - 1) {                                                          // PA:1349-1361, :1699
         const double v_gradw_b = v1 * gw1_k1 + v2 * gw2_k1;                         // v_i(nlevp) = v(nlev)
         const double w_tens_b = (-w_vadv_b - v_gradw_b) * s1 - s1 * G_GRAV * (1 - mu_k1);
@@ -422,14 +423,26 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   if (accum) {
     __syncthreads();
     if (tid < 16) {
+      // two running sums in the reference's k order; eight addends are loaded ahead of the dependent additions
       double pi_i = A.prm.ptop, om_i = 0.0;
-      for (int k = 0; k < nlev; k++) {
-        const double dp = sdp[k * 16 + tid], dv = sdiv[k * 16 + tid];
-        spnh[k * 16 + tid] = pi_i + dp / 2;                 // pi(k)
-        const double om_next = om_i + dv;
-        sdiv[k * 16 + tid] = (om_i + om_next) / 2;
-        pi_i = pi_i + dp;
-        om_i = om_next;
+      for (int k0 = 0; k0 < nlev; k0 += 8) {
+        double xd[8], xv[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const int k = k0 + i < nlev ? k0 + i : nlev - 1;
+          xd[i] = sdp[k * 16 + tid]; xv[i] = sdiv[k * 16 + tid];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const int k = k0 + i;
+          if (k < nlev) {
+            spnh[k * 16 + tid] = pi_i + xd[i] / 2;              // pi(k)
+            const double om_next = om_i + xv[i];
+            sdiv[k * 16 + tid] = (om_i + om_next) / 2;
+            pi_i = pi_i + xd[i];
+            om_i = om_next;
+          }
+        }
       }
     }
     __syncthreads();
@@ -441,30 +454,35 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
         const double vgrad_p = sv[k * 32 + p] * g1 + sv[k * 32 + 16 + p] * g2;
         const double omega = vgrad_p - sdiv[k * 16 + p];
         A.der.omega_p[(size_t)ie * 16 * nlev + k * 16 + p] += A.eta_ave_w * omega;
+        const size_t gqv = (size_t)ie * 32 * nlev + k * 32 + p;
+        const double dpk = sdp[k * 16 + p];
+        A.der.vn0[gqv] += A.eta_ave_w * (sv[k * 32 + p] * dpk);                     // PA:1190
+        A.der.vn0[gqv + 16] += A.eta_ave_w * (sv[k * 32 + 16 + p] * dpk);
       }
     }
   }
 }
 
-template <int FORM, bool PGRAD, bool ACCUM, bool VADV>
+template <int FORM, bool PGRAD, bool ACCUM, bool VADV, bool SAVE>
 static void launch_caar_pre_t(const CaarArgs &A, cudaStream_t st)
 {
   const size_t sm = caar_smem_bytes(A.prm.nlev, VADV);
   static size_t configured = 0;
   if (sm > configured) {
-    cudaFuncSetAttribute(caar_pre_kernel<FORM, PGRAD, ACCUM, VADV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaFuncSetAttribute(caar_pre_kernel<FORM, PGRAD, ACCUM, VADV, SAVE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     configured = sm;
   }
   const int nb = A.elist ? A.ecount : A.prm.nelem;
-  if (nb > 0) caar_pre_kernel<FORM, PGRAD, ACCUM, VADV><<<nb, CAAR_THREADS, sm, st>>>(A);
+  if (nb > 0) caar_pre_kernel<FORM, PGRAD, ACCUM, VADV, SAVE><<<nb, CAAR_THREADS, sm, st>>>(A);
 }
 
 template <int FORM, bool PGRAD>
 static void launch_caar_pre_a(const CaarArgs &A, cudaStream_t st)
 {
-  const bool acc = A.eta_ave_w != 0.0, vadv = A.prm.rsplit == 0;
-  if (vadv) { acc ? launch_caar_pre_t<FORM, PGRAD, true, true>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, true>(A, st); }
-  else { acc ? launch_caar_pre_t<FORM, PGRAD, true, false>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, false>(A, st); }
+  const bool acc = A.eta_ave_w != 0.0, vadv = A.prm.rsplit == 0, save = A.ew != nullptr && !vadv;
+  if (vadv) { acc ? launch_caar_pre_t<FORM, PGRAD, true, true, false>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, true, false>(A, st); }
+  else if (save) { acc ? launch_caar_pre_t<FORM, PGRAD, true, false, true>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, false, true>(A, st); }
+  else { acc ? launch_caar_pre_t<FORM, PGRAD, true, false, false>(A, st) : launch_caar_pre_t<FORM, PGRAD, false, false, false>(A, st); }
 }
 
 void launch_caar_pre(const CaarArgs &A, cudaStream_t st)

@@ -14,6 +14,9 @@ struct CaarArgs {
   Params prm;
   double dt2, eta_ave_w, scale1, scale2, scale3;
   int *err;
+  // optional: the explicit stiff terms of state(n0) that a later DIRK stage adds (IM:176-205), saved here so that
+  // stage does not have to redo the EOS of this state: ew = dpnh_dp_i - 1, ephi = g w_i - gwphis, [ie][k<nlev][16]
+  double *ew = nullptr, *ephi = nullptr;
 };
 
 struct DssArgs {
@@ -31,6 +34,8 @@ struct DirkArgs {
   Geo geo;
   Params prm;
   double dt2, alphadt_n0, alphadt_nm1;
+  // optional: explicit terms of state(n0) / state(nm1) saved by the CAAR launches that evaluated those states
+  const double *ew_n0 = nullptr, *ephi_n0 = nullptr, *ew_nm1 = nullptr, *ephi_nm1 = nullptr;
   int *err;
   int *max_iter;            // running max of itercount over elements (atomicMax)
   unsigned long long *max_deltaerr_bits;   // running max of deltaerr (as ordered bits)
