@@ -74,6 +74,7 @@ struct Session {
   bool have_forcing = false;
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
   int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
+  int fuse_combo = 1;       // THETAL_B200_FUSE_COMBO=0: separate combo_kernel launch for the tstep_type 9 combination
   int expl_cache = 1;       // THETAL_B200_EXPL_CACHE=0: the closing DIRK stage redoes the EOS of state(n0), state(nm1)
   int overlap = 1;          // halo of a DSS travels while the producer runs on the interior elements
   // device
@@ -162,6 +163,7 @@ void initialize_hommexx_session(void)
   CUDA_OK(cudaSetDevice(S.device % ndev));
   CUDA_OK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
   if (getenv("THETAL_B200_EXPL_CACHE")) S.expl_cache = atoi(getenv("THETAL_B200_EXPL_CACHE"));
+  if (getenv("THETAL_B200_FUSE_COMBO")) S.fuse_combo = atoi(getenv("THETAL_B200_FUSE_COMBO"));
   CUDA_OK(cudaEventCreate(&S.ev0));
   CUDA_OK(cudaEventCreate(&S.ev1));
   if (S.nranks > 1) {
@@ -665,7 +667,8 @@ template <class F> void produce_and_exchange(const StatePtrs &t, int nk, int wbo
 // ---- the pieces of prim_advance_exp, enqueued on S.stream --------------------------------
 // save_expl: 0 = no, 1 / 2 = keep the explicit stiff terms of state(n0) for the closing DIRK stage of this step in the
 // (otherwise idle) hyperviscosity scratch tensB: w/phi slots (1) or dp/th slots (2)
-void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3, int save_expl = 0)
+void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3, int save_expl = 0,
+              int combo_b = -1, int combo_c = -1)
 {
   Nvtx r("compute_andor_apply_rhs");
   CaarArgs a;
@@ -683,6 +686,7 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
   d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
   d.do_limiter = (s3 != 0.0);
   d.elist = nullptr; d.ecount = 0;
+  if (combo_b >= 0) { d.combo_b = S.tl[combo_b]; d.combo_c = S.tl[combo_c]; }    // PA:313-326 fused behind the DSS
   { ProfScope ps(1); launch_caar_dss_post(d, S.stream); }
   S.launches += 2;
 }
@@ -792,8 +796,8 @@ void run_prim_advance_exp(double dt, int nm1, int n0, int np1)
       run_caar(np1, n0, nm1, dt / 5, 0.0, 1, 0, 1, 2);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 5);
       run_caar(np1, n0, np1, dt / 3, 0.0, 1, 0, 1);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 3);
       run_caar(np1, n0, np1, 2 * dt / 3, 0.0, 1, 0, 1);       run_dirk(nm1, 0.0, n0, 0.0, np1, 2 * dt / 3);
-      run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1);
-      run_combo(9, np1, nm1, n0);
+      if (S.fuse_combo) run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1, 0, nm1, n0);
+      else { run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1); run_combo(9, np1, nm1, n0); }
       const double a1 = 5 * dt / 18, a2 = dt / 36, a3 = 8 * dt / 18;
       run_dirk(nm1, a2, n0, a1, np1, a3, true);     // neither state(n0) nor state(nm1) changed since stages 1 and 2
       break;

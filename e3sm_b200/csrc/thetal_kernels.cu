@@ -409,7 +409,11 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       A.tens.w[gqi] = spheremp * (s3 * m_w + dt2 * w_tens);
       A.tens.phi[gqi] = spheremp * (s3 * m_phi + dt2 * phi_tens);
       A.tens.dp[gq] = spheremp * (s3 * m_dp - s1 * dt2 * (VADV ? divdp + deta : divdp));   // PA:1693-1694
-      if (accum) sdiv[q] = divdp;          // derived%vn0, omega_p are accumulated after the loop (phase 3/4)
+      if (accum) {
+        sdiv[q] = divdp;
+        A.der.vn0[gqv] += A.eta_ave_w * (v1 * dp);                                  // PA:1190
+        A.der.vn0[gqv + 16] += A.eta_ave_w * (v2 * dp);
+      }
       if (k == nlev - 1) {                                                          // PA:1349-1361, :1699
         const double v_gradw_b = v1 * gw1_k1 + v2 * gw2_k1;                         // v_i(nlevp) = v(nlev)
         const double w_tens_b = (-w_vadv_b - v_gradw_b) * s1 - s1 * G_GRAV * (1 - mu_k1);
@@ -421,28 +425,18 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
 
   // ---- phase 3/4: diagnostic omega (PA:1197-1213, 1312-1313), only when eta_ave_w != 0 ----
   if (accum) {
+    // (moving the vn0 read-modify-writes here, or requesting the old accumulator values ahead of the scans,
+    //  was measured slower on C2: 419 and 431 us against 404 us per launch)
     __syncthreads();
     if (tid < 16) {
-      // two running sums in the reference's k order; eight addends are loaded ahead of the dependent additions
       double pi_i = A.prm.ptop, om_i = 0.0;
-      for (int k0 = 0; k0 < nlev; k0 += 8) {
-        double xd[8], xv[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          const int k = k0 + i < nlev ? k0 + i : nlev - 1;
-          xd[i] = sdp[k * 16 + tid]; xv[i] = sdiv[k * 16 + tid];
-        }
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          const int k = k0 + i;
-          if (k < nlev) {
-            spnh[k * 16 + tid] = pi_i + xd[i] / 2;              // pi(k)
-            const double om_next = om_i + xv[i];
-            sdiv[k * 16 + tid] = (om_i + om_next) / 2;
-            pi_i = pi_i + xd[i];
-            om_i = om_next;
-          }
-        }
+      for (int k = 0; k < nlev; k++) {
+        const double dp = sdp[k * 16 + tid], dv = sdiv[k * 16 + tid];
+        spnh[k * 16 + tid] = pi_i + dp / 2;                 // pi(k)
+        const double om_next = om_i + dv;
+        sdiv[k * 16 + tid] = (om_i + om_next) / 2;
+        pi_i = pi_i + dp;
+        om_i = om_next;
       }
     }
     __syncthreads();
@@ -454,10 +448,6 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
         const double vgrad_p = sv[k * 32 + p] * g1 + sv[k * 32 + 16 + p] * g2;
         const double omega = vgrad_p - sdiv[k * 16 + p];
         A.der.omega_p[(size_t)ie * 16 * nlev + k * 16 + p] += A.eta_ave_w * omega;
-        const size_t gqv = (size_t)ie * 32 * nlev + k * 32 + p;
-        const double dpk = sdp[k * 16 + p];
-        A.der.vn0[gqv] += A.eta_ave_w * (sv[k * 32 + p] * dpk);                     // PA:1190
-        A.der.vn0[gqv + 16] += A.eta_ave_w * (sv[k * 32 + 16 + p] * dpk);
       }
     }
   }
@@ -543,6 +533,52 @@ __device__ void limiter_columns(const StatePtrs &out, int ie, int nlev, int p, d
 
 constexpr int DSS_THREADS = 256;
 
+// tstep_type 9 closing combination (PA:313-326): a(np1) += (b(nm1) - c(n0))/4 for one element, then limiter_dp3d_k.
+// Called by all DSS_THREADS threads of the CTA that owns element ie.
+__device__ __forceinline__ void combo9_element(const StatePtrs &a, const StatePtrs &b, const StatePtrs &c, const Geo &geo,
+                                               const Params &prm, int ie, int tid)
+{
+  const int nlev = prm.nlev, nlevp = nlev + 1, p = tid & 15, kslot = tid >> 4;
+  constexpr int KS = DSS_THREADS / 16;
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
+  int lim_dp = 0, lim_th = 0;
+  for (int k = kslot; k < nlevp; k += KS) {
+    const int q = k * 16 + p;
+    a.w[ei + q] = a.w[ei + q] + (b.w[ei + q] - c.w[ei + q]) / 4;
+    if (k < nlev) {
+      const size_t qv = ev + k * 32 + p;
+      a.v[qv] = a.v[qv] + (b.v[qv] - c.v[qv]) / 4;
+      a.v[qv + 16] = a.v[qv + 16] + (b.v[qv + 16] - c.v[qv + 16]) / 4;
+      const double th = a.th[em + q] + (b.th[em + q] - c.th[em + q]) / 4;
+      const double dp = a.dp[em + q] + (b.dp[em + q] - c.dp[em + q]) / 4;
+      a.th[em + q] = th; a.dp[em + q] = dp;
+      a.phi[ei + q] = a.phi[ei + q] + (b.phi[ei + q] - c.phi[ei + q]) / 4;
+      if (dp < prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
+      if (th - prm.vtheta_thresh * dp < 0) lim_th = 1;
+    }
+  }
+  lim_dp = __syncthreads_or(lim_dp);                                                // PA:324-325
+  if (lim_dp) {
+    __threadfence_block();
+    if (tid < 16) limiter_columns(a, ie, nlev, tid, geo.spheremp[(size_t)ie * 16 + tid], prm.dp3d_thresh);
+    __threadfence_block();
+    __syncthreads();
+    lim_th = 0;
+    for (int k = kslot; k < nlev; k += KS) {
+      const size_t q = em + (size_t)k * 16 + p;
+      if (a.th[q] - prm.vtheta_thresh * a.dp[q] < 0) lim_th = 1;
+    }
+  }
+  lim_th = __syncthreads_or(lim_th);
+  if (lim_th) {
+    for (int k = kslot; k < nlev; k += KS) {
+      const size_t q = em + (size_t)k * 16 + p;
+      const double dp = a.dp[q];
+      if (a.th[q] - prm.vtheta_thresh * dp < 0) a.th[q] = prm.vtheta_thresh * dp;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const DssArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
@@ -591,7 +627,7 @@ __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const Dss
     if (dp < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
     if (th - A.prm.vtheta_thresh * dp < 0) lim_th = 1;
   }
-  if (!A.do_limiter) return;
+  if (A.do_limiter) {
   // limiter_dp3d_k: rare; block-uniform decision
   lim_dp = __syncthreads_or(lim_dp);
   if (lim_dp) {
@@ -612,6 +648,14 @@ __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const Dss
       const double dp = A.out.dp[q];
       if (A.out.th[q] - A.prm.vtheta_thresh * dp < 0) A.out.th[q] = A.prm.vtheta_thresh * dp;
     }
+  }
+  }
+  // the tstep_type 9 combination that follows the last stage (PA:313-326) is applied to the element this CTA has
+  // just finished, while its columns are still in L2: np1 is not streamed through HBM a second time
+  if (A.combo_b.v) {
+    __threadfence_block();
+    __syncthreads();
+    combo9_element(A.out, A.combo_b, A.combo_c, A.geo, A.prm, ie, tid);
   }
 }
 
@@ -1365,15 +1409,16 @@ __global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A
     const double tv2 = dt * dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2) * rs;
     const double dp_old = A.st.dp[em + q];
     const double theta_old = A.th_is_theta ? A.st.th[em + q] : div_fast(A.st.th[em + q], dp_old);
-    // remove/add reference state exactly as PA:629-647 does (rounding of (x-r)+r)
-    const double dref = A.ref.dp_ref[em + q], tref = A.ref.theta_ref[em + q], pref = A.ref.phi_ref[ei + q];
-    const double dp_new = ((dp_old - dref) + dref) + tdp;
-    const double theta_new = ((theta_old - tref) + tref) + tth;
+    // PA:629-647 subtracts the reference state before the laplacians and adds it back afterwards; the state itself
+    // differs from (x - r) + r by at most one rounding of x, far below the parity budget, so the three reference
+    // fields are not read again here (27.8 KB per element and subcycle at L72)
+    const double dp_new = dp_old + tdp;
+    const double theta_new = theta_old + tth;
     const double v1 = A.st.v[ev + ov + p] + tv1, v2 = A.st.v[ev + ov + 16 + p] + tv2;
     A.st.v[ev + ov + p] = v1; A.st.v[ev + ov + 16 + p] = v2;
     A.st.w[ei + q] = A.st.w[ei + q] + tw;
     A.st.dp[em + q] = dp_new;
-    A.st.phi[ei + q] = ((A.st.phi[ei + q] - pref) + pref) + tph;
+    A.st.phi[ei + q] = A.st.phi[ei + q] + tph;
     A.st.th[em + q] = A.last_subcycle ? theta_new * dp_new : theta_new;
     if (A.last_subcycle && k == nlev - 1) {
       const double g1 = A.geo.gradphis[(size_t)ie * 32 + p], g2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
@@ -1459,56 +1504,20 @@ void launch_hv(int which, const HvArgs &A, cudaStream_t st)
 __global__ void __launch_bounds__(DSS_THREADS) combo_kernel(const ComboArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = blockIdx.x, tid = threadIdx.x;
+  if (A.kind == 9) { combo9_element(A.a, A.b, A.c, A.geo, A.prm, ie, tid); return; }
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = DSS_THREADS / 16;
   const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
-  int lim_dp = 0, lim_th = 0;
-  for (int k = kslot; k < nlevp; k += KS) {
+  for (int k = kslot; k < nlevp; k += KS) {                                         // tstep_type 5, PA:197-208
     const int q = k * 16 + p;
-    if (A.kind == 9) {
-      A.a.w[ei + q] = A.a.w[ei + q] + (A.b.w[ei + q] - A.c.w[ei + q]) / 4;
-      if (k < nlev) {
-        const size_t qv = ev + k * 32 + p;
-        A.a.v[qv] = A.a.v[qv] + (A.b.v[qv] - A.c.v[qv]) / 4;
-        A.a.v[qv + 16] = A.a.v[qv + 16] + (A.b.v[qv + 16] - A.c.v[qv + 16]) / 4;
-        const double th = A.a.th[em + q] + (A.b.th[em + q] - A.c.th[em + q]) / 4;
-        const double dp = A.a.dp[em + q] + (A.b.dp[em + q] - A.c.dp[em + q]) / 4;
-        A.a.th[em + q] = th; A.a.dp[em + q] = dp;
-        A.a.phi[ei + q] = A.a.phi[ei + q] + (A.b.phi[ei + q] - A.c.phi[ei + q]) / 4;
-        if (dp < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
-        if (th - A.prm.vtheta_thresh * dp < 0) lim_th = 1;
-      }
-    } else {
-      A.a.w[ei + q] = (5 * A.a.w[ei + q] - A.b.w[ei + q]) / 4;
-      if (k < nlev) {
-        const size_t qv = ev + k * 32 + p;
-        A.a.v[qv] = (5 * A.a.v[qv] - A.b.v[qv]) / 4;
-        A.a.v[qv + 16] = (5 * A.a.v[qv + 16] - A.b.v[qv + 16]) / 4;
-        A.a.th[em + q] = (5 * A.a.th[em + q] - A.b.th[em + q]) / 4;
-        A.a.dp[em + q] = (5 * A.a.dp[em + q] - A.b.dp[em + q]) / 4;
-        A.a.phi[ei + q] = (5 * A.a.phi[ei + q] - A.b.phi[ei + q]) / 4;
-      }
-    }
-  }
-  if (A.kind != 9) return;
-  lim_dp = __syncthreads_or(lim_dp);                                                // PA:324-325
-  if (lim_dp) {
-    __threadfence_block();
-    if (tid < 16) limiter_columns(A.a, ie, nlev, tid, A.geo.spheremp[(size_t)ie * 16 + tid], A.prm.dp3d_thresh);
-    __threadfence_block();
-    __syncthreads();
-    lim_th = 0;
-    for (int k = kslot; k < nlev; k += KS) {
-      const size_t q = em + (size_t)k * 16 + p;
-      if (A.a.th[q] - A.prm.vtheta_thresh * A.a.dp[q] < 0) lim_th = 1;
-    }
-  }
-  lim_th = __syncthreads_or(lim_th);
-  if (lim_th) {
-    for (int k = kslot; k < nlev; k += KS) {
-      const size_t q = em + (size_t)k * 16 + p;
-      const double dp = A.a.dp[q];
-      if (A.a.th[q] - A.prm.vtheta_thresh * dp < 0) A.a.th[q] = A.prm.vtheta_thresh * dp;
+    A.a.w[ei + q] = (5 * A.a.w[ei + q] - A.b.w[ei + q]) / 4;
+    if (k < nlev) {
+      const size_t qv = ev + k * 32 + p;
+      A.a.v[qv] = (5 * A.a.v[qv] - A.b.v[qv]) / 4;
+      A.a.v[qv + 16] = (5 * A.a.v[qv + 16] - A.b.v[qv + 16]) / 4;
+      A.a.th[em + q] = (5 * A.a.th[em + q] - A.b.th[em + q]) / 4;
+      A.a.dp[em + q] = (5 * A.a.dp[em + q] - A.b.dp[em + q]) / 4;
+      A.a.phi[ei + q] = (5 * A.a.phi[ei + q] - A.b.phi[ei + q]) / 4;
     }
   }
 }

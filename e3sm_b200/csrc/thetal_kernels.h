@@ -27,6 +27,7 @@ struct DssArgs {
   int do_limiter;
   const int *elist;         // optional element list; null = all
   int ecount;
+  StatePtrs combo_b{}, combo_c{};   // tstep_type 9 closing stage: out += (combo_b - combo_c)/4 fused behind the DSS (v == null: off)
 };
 
 struct DirkArgs {
