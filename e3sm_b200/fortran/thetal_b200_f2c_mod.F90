@@ -86,6 +86,21 @@ module thetal_b200_f2c_mod
     subroutine thetal_b200_sync() bind(c)
     end subroutine thetal_b200_sync
 
+    ! ---- plain theta-l build: state inside the array of element structs (element_mod.F90:32-144) ----
+    ! call init_elements_states_strided_c(c_loc(elem(1)%state%v), c_loc(elem(1)%state%w_i), ..., &
+    !                                     int(storage_size(elem(1))/8, c_long))
+    subroutine init_elements_states_strided_c(v, w_i, vtheta_dp, phinh_i, dp3d, elem_stride_bytes) bind(c)
+      import :: c_ptr, c_long
+      type(c_ptr), intent(in) :: v, w_i, vtheta_dp, phinh_i, dp3d
+      integer(c_long), intent(in) :: elem_stride_bytes
+    end subroutine init_elements_states_strided_c
+
+    subroutine apply_cam_forcing_dynamics_c(nt, dt) bind(c)                               ! prim_advance_mod.F90:517
+      import :: c_int, c_double
+      integer(c_int), intent(in) :: nt
+      real(c_double), intent(in) :: dt
+    end subroutine apply_cam_forcing_dynamics_c
+
   end interface
 
 contains
