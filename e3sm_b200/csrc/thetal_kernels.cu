@@ -275,6 +275,8 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     const size_t gqi = (size_t)ie * 16 * nlevp + q;
     const double m_v1 = A.nm1.v[gqv], m_v2 = A.nm1.v[gqv + 16], m_th = A.nm1.th[gq];
     const double m_w = A.nm1.w[gqi], m_phi = A.nm1.phi[gqi], m_dp = A.nm1.dp[gq];
+    double o_vn1 = 0.0, o_vn2 = 0.0;         // derived%vn0 before this stage: requested with the nm1 values
+    if (ACCUM) { o_vn1 = A.der.vn0[gqv]; o_vn2 = A.der.vn0[gqv + 16]; }
     const double dp = sdp[q], th = sth[q], v1 = sv[k * 32 + p], v2 = sv[k * 32 + 16 + p];
     const double wk = sw[q], wk1 = sw[q + 16];
     const double pnh = spnh[q], exner = sexn[q];
@@ -411,8 +413,8 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       A.tens.dp[gq] = spheremp * (s3 * m_dp - s1 * dt2 * (VADV ? divdp + deta : divdp));   // PA:1693-1694
       if (accum) {
         sdiv[q] = divdp;
-        A.der.vn0[gqv] += A.eta_ave_w * (v1 * dp);                                  // PA:1190
-        A.der.vn0[gqv + 16] += A.eta_ave_w * (v2 * dp);
+        A.der.vn0[gqv] = o_vn1 + A.eta_ave_w * (v1 * dp);                           // PA:1190
+        A.der.vn0[gqv + 16] = o_vn2 + A.eta_ave_w * (v2 * dp);
       }
       if (k == nlev - 1) {                                                          // PA:1349-1361, :1699
         const double v_gradw_b = v1 * gw1_k1 + v2 * gw2_k1;                         // v_i(nlevp) = v(nlev)
@@ -425,29 +427,49 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
 
   // ---- phase 3/4: diagnostic omega (PA:1197-1213, 1312-1313), only when eta_ave_w != 0 ----
   if (accum) {
-    // (moving the vn0 read-modify-writes here, or requesting the old accumulator values ahead of the scans,
-    //  was measured slower on C2: 419 and 431 us against 404 us per launch)
+    // (moving the vn0 read-modify-writes behind the level loop was measured slower on C2; their old values are
+    //  requested at the top of each level instead, and the omega_p ones one iteration ahead)
     __syncthreads();
-    if (tid < 16) {
+    {
+      // pi_i(k+1) = pi_i(k) + dp3d(k), omega_i(k+1) = omega_i(k) + divdp(k) (PA:1197-1202) as a two-level scan over
+      // all 256 threads: half-warp c sums its chunk of levels, the chunk totals are combined through shared
+      // memory.  (The association differs from the serial sum by roundings of 1e-16; omega_p is a diagnostic.)
+      const int CH = (nlev + KS - 1) / KS, kb = kslot * CH;
+      double *stot = sdiv + 16 * nlev;                       // scratch tiles are free after the level loop
+      double sd = 0.0, sv_ = 0.0;
+      for (int i = 0; i < CH; i++) {
+        const int k = kb + i;
+        if (k < nlev) { sd = sd + sdp[k * 16 + p]; sv_ = sv_ + sdiv[k * 16 + p]; }
+      }
+      stot[kslot * 16 + p] = sd; stot[256 + kslot * 16 + p] = sv_;
+      __syncthreads();
       double pi_i = A.prm.ptop, om_i = 0.0;
-      for (int k = 0; k < nlev; k++) {
-        const double dp = sdp[k * 16 + tid], dv = sdiv[k * 16 + tid];
-        spnh[k * 16 + tid] = pi_i + dp / 2;                 // pi(k)
-        const double om_next = om_i + dv;
-        sdiv[k * 16 + tid] = (om_i + om_next) / 2;
-        pi_i = pi_i + dp;
-        om_i = om_next;
+      for (int c = 0; c < kslot; c++) { pi_i = pi_i + stot[c * 16 + p]; om_i = om_i + stot[256 + c * 16 + p]; }
+      for (int i = 0; i < CH; i++) {
+        const int k = kb + i;
+        if (k < nlev) {
+          const double dp = sdp[k * 16 + p], dv = sdiv[k * 16 + p];
+          spnh[k * 16 + p] = pi_i + dp / 2;                 // pi(k), PA:1204
+          const double om_next = om_i + dv;
+          sdiv[k * 16 + p] = (om_i + om_next) / 2;
+          pi_i = pi_i + dp;
+          om_i = om_next;
+        }
       }
     }
     __syncthreads();
+    double *gom = A.der.omega_p + (size_t)ie * 16 * nlev;
+    double o_next = kslot < nlev ? gom[kslot * 16 + p] : 0.0;      // old value one iteration ahead of its use
     for (int it = 0; it < niter; it++) {
       const int k = it * KS + kslot;
+      const double o_om = o_next;
+      if (k + KS < nlev) o_next = gom[(k + KS) * 16 + p];
       if (k < nlev) {
         double g1, g2;
         gradient_sphere(t, spnh + k * 16, g1, g2);
         const double vgrad_p = sv[k * 32 + p] * g1 + sv[k * 32 + 16 + p] * g2;
         const double omega = vgrad_p - sdiv[k * 16 + p];
-        A.der.omega_p[(size_t)ie * 16 * nlev + k * 16 + p] += A.eta_ave_w * omega;
+        gom[k * 16 + p] = o_om + A.eta_ave_w * omega;                                   // PA:1312-1313
       }
     }
   }
