@@ -1173,6 +1173,9 @@ __device__ __forceinline__ void ptw_init(PtW &w, const Pt &t, const Geo &g, int 
 
 constexpr int HV_THREADS = 256;
 constexpr int HV_SLOTS = 18;
+#ifndef HV_MINB
+#define HV_MINB 2
+#endif
 
 // Laplacians of the six fields of one level (scalar: DM:1072-1119 with var_coef=.false.;
 // vector: DM:1212-1251).  All 16 lanes of the half-warp must call this together.
@@ -1285,7 +1288,7 @@ __device__ __forceinline__ void vlaplace_cartesian(const Pt &t, const PtW &w, co
 __host__ __device__ inline size_t hv_smem_bytes() { return sizeof(double) * (HV_THREADS / 16) * HV_SLOTS * 16; }
 
 // pass 1 (PA:629-636 + VT:93-107): laplacians of (state - reference state) -> tout
-__global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace1_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, HV_MINB) hv_laplace1_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
@@ -1343,7 +1346,7 @@ __global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace1_kernel(const HvArgs
 
 // pass 2 (VT:134-164 + PA:657-663): DSS(tin) * rspheremp -> laplacian again -> * (-nu) -> tout
 template <bool TENSOR>
-__global__ void __launch_bounds__(HV_THREADS, 2) hv_laplace2_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, HV_MINB) hv_laplace2_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
