@@ -607,3 +607,29 @@ def test_ps_v_and_initialize_dp3d_from_ps(case_c1, parity_state_c1):
     assert rel_l2(back[:, 1], ps[:, 1]) <= 1e-14                          # sum of the new layers = ps_v again
     assert rel_l2(back[:, 0], hv.hyai[0] * hv.ps0 + st.dp3d[:, 0].sum(axis=1)) <= 1e-15
     d.close()
+
+
+# ---------------------------------------------------------------- the real C2 / C5 sphere
+@pytest.mark.parametrize("cfg", ["C2", "C5"])
+def test_one_step_on_the_real_ne30_sphere(cfg):
+    """BASELINE config 2 (and 5: hypervis_subcycle 3, nu_div 2.5e15) at its real size, ne30np4 L72, 5400 elements:
+    one full dynamics step from the JW state advanced two steps (so w != 0), GPU vs oracle, rel-L2 <= 1e-10."""
+    from e3sm_b200.dycore import build_case
+    from e3sm_b200.params import config
+    p = config(cfg)
+    assert p.ne == 30 and p.nlev == 72
+    case = (p,) + build_case(p)
+    p, o, so, d = make_pair(case, case[3].copy())
+    nm1, n0, np1 = 0, 1, 2
+    for _ in range(3):
+        o.prim_advance_exp(p.tstep, nm1, n0, np1)
+        d.prim_advance_exp(p.tstep, nm1, n0, np1)
+        nm1, n0, np1 = n0, np1, nm1
+    assert o.error_flag == 0
+    sg = d.get_state()
+    for f in ("v", "vtheta_dp", "phinh_i", "dp3d"):
+        r = rel_l2(getattr(sg, f)[:, n0], getattr(so, f)[:, n0])
+        assert r <= TOL, (cfg, f, r)
+    dw = float(np.abs(sg.w_i[:, n0] - so.w_i[:, n0]).max())
+    assert dw <= 1e-10 * max(1.0, float(np.abs(so.w_i[:, n0]).max())), dw
+    d.close()

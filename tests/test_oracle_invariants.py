@@ -254,3 +254,21 @@ def test_oracle_matches_regression_fixture():
     from make_golden import oracle_run
     st, tl, diag = oracle_run()
     _check_against_fixture(st, tl, diag, 1e-12)
+
+
+def test_fma_contraction_spread_of_the_oracle(case_c1, parity_state_c1):
+    """the realistic floor for "matches Fortran".  The same oracle source built with FMA contraction and
+    -O3 -march=x86-64-v3 (libthetal_oracle_fast.so) against the -O2 -ffp-contract=off build: one full tstep_type 9
+    step differs by rounding only, orders of magnitude inside the 1e-10 parity budget."""
+    from oracle.oracle import Oracle
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    sa, sb = parity_state_c1.copy(), parity_state_c1.copy()
+    oa = Oracle(grid, hv, p, phis, gradphis, refs, sa, nthreads=2)
+    ob = Oracle(grid, hv, p, phis, gradphis, refs, sb, nthreads=2, fast=True)
+    oa.prim_advance_exp(p.tstep, 0, 1, 2)
+    ob.prim_advance_exp(p.tstep, 0, 1, 2)
+    worst = {}
+    for f in ("v", "w_i", "vtheta_dp", "phinh_i", "dp3d"):
+        worst[f] = rel_l2(getattr(sb, f)[:, 2], getattr(sa, f)[:, 2])
+    print("FMA/no-FMA spread after one step:", worst)
+    assert max(worst.values()) <= 1e-11 and max(worst.values()) > 0
