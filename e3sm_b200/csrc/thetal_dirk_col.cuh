@@ -58,15 +58,6 @@ __device__ __forceinline__ double group_min(double v)
   return v;
 }
 
-// x / 1e5 to <= 1 ulp without a reciprocal instruction (P0 is a constant)
-__device__ __forceinline__ double div_p0(double x)
-{
-  constexpr double c = 1.0 / P0;
-  const double q = x * c;
-  const double rem = fma(-q, P0, x);
-  return fma(rem, c, q);
-}
-
 // IM:42-53 at one interface from the two adjacent levels
 __device__ __forceinline__ double gwphis_of(double dk, double dm, double v1k, double v1m, double v2k, double v2m,
                                             double g1, double g2, double hyb)

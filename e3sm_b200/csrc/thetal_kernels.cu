@@ -147,9 +147,22 @@ static_assert(1.0 / (1.0 - KAPPA) == 1.3997994317232159 && KAPPA - 1.0 == -0.714
 using thetal_pow::div_fast;
 using thetal_pow::rcp_fast;
 
+// a/d given r = rcp_fast(d): the same two operations div_fast ends with, so a/d == div_fast(a, d) bit for bit
+__device__ __forceinline__ double div_by(double a, double d, double r)
+{
+  const double q = a * r;
+  return fma(fma(-q, d, a), r, q);
+}
+// x / 1e5 to <= 1 ulp without a reciprocal instruction (P0 is a constant)
+__device__ __forceinline__ double div_p0(double x)
+{
+  constexpr double c = 1.0 / P0;
+  const double q = x * c;
+  return fma(fma(-q, P0, x), c, q);
+}
 __device__ __forceinline__ double eos_pnh(double p_over_exner)
 {
-  return P0 * thetal_pow::pow_pos(div_fast(p_over_exner, P0), C_GAMMA);
+  return P0 * thetal_pow::pow_pos(div_p0(p_over_exner), C_GAMMA);
 }
 
 // ==========================================================================================
@@ -289,9 +302,10 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     } else {
       const double dpm = sdp[q - 16];
       dpi_k = (dp + dpm) / 2;
-      v1i_k = div_fast(dp * v1 + dpm * sv[(k - 1) * 32 + p], 2 * dpi_k);
-      v2i_k = div_fast(dp * v2 + dpm * sv[(k - 1) * 32 + 16 + p], 2 * dpi_k);
-      mu_k = div_fast(pnh - spnh[q - 16], dpi_k);
+      const double r2 = thetal_pow::rcp_fast(2 * dpi_k);          // one reciprocal for the three quotients:
+      v1i_k = div_by(dp * v1 + dpm * sv[(k - 1) * 32 + p], 2 * dpi_k, r2);
+      v2i_k = div_by(dp * v2 + dpm * sv[(k - 1) * 32 + 16 + p], 2 * dpi_k, r2);
+      mu_k = div_by(pnh - spnh[q - 16], dpi_k, 2 * r2);           // 1/dpi = 2/(2 dpi), exact scaling
     }
     double mu_k1;
     if (k == nlev - 1) mu_k1 = div_fast(2 * ((pnh + dp / 2) - pnh), dp);             // EOS:193,205
@@ -397,8 +411,9 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
       double gl1, gl2;
       gradient_sphere(t, scr, gl1, gl2);
       const double T0 = TREF - TREF_LAPSE * TREF * CP / G_GRAV;
-      mg1 = mg1 + CP * T0 * (gl1 - div_fast(ge1, exner));
-      mg2 = mg2 + CP * T0 * (gl2 - div_fast(ge2, exner));
+      const double rex = thetal_pow::rcp_fast(exner);
+      mg1 = mg1 + CP * T0 * (gl1 - div_by(ge1, exner, rex));
+      mg2 = mg2 + CP * T0 * (gl2 - div_by(ge2, exner, rex));
     }
     const double vt1 = (-vv1 + v2 * (fcor + vort) - ke1 - mg1 - gp1 - wv1) * s1;    // PA:1495-1506
     const double vt2 = (-vv2 - v1 * (fcor + vort) - ke2 - mg2 - gp2 - wv2) * s1;
