@@ -316,7 +316,9 @@ def run_ours(args, world, rank, local, td):
     Dv = 128 * (4 * nlev + 1)
     bstep = bytes_per_element_step(p, d.nlev_tom)
     # algorithmic bytes per launch of each family, tstep_type 9: 5 launches each
-    alg = {"caar_pre": (14 * S + 4 * Dv) / 5.0, "caar_dss_post": 2 * S, "dirk": (7 * S + 10 * I) / 5.0}
+    # (the tstep_type 9 combination, 4S, is fused behind the fifth DSS/post launch)
+    alg = {"caar_pre": (14 * S + 4 * Dv) / 5.0, "caar_dss_post": (10 * S + (4 * S if p.tstep_type == 9 else 0)) / 5.0,
+           "dirk": (7 * S + 10 * I) / 5.0}
     nl = {"caar_pre": 5, "caar_dss_post": 5, "dirk": 5}
     kname = {"caar_pre": "caar_pre_kernel", "caar_dss_post": "caar_dss_post_kernel", "dirk": "dirk_col_kernel"}
     dom = max(nl, key=lambda k: fam_ms[k])
