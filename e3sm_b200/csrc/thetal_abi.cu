@@ -945,6 +945,36 @@ void apply_cam_forcing_dynamics_c(const int *nt, const double *dt)
   thetal_b200_sync();
 }
 
+// Addition: DSS of a caller's field, field(np,np,nlayers,nelemd) in place: every node ends with the sum
+// over the elements that share it, in the Fortran unpack order (edge_mod.F90:888-941), across ranks included.
+void dss_c(thetal_f90ptr_out field, const int *nlayers)
+{
+  REQUIRE(S.device_ready && field && *field, "dss_c before init_functors_c");
+  const int nl = *nlayers, n = S.prm.nelem;
+  REQUIRE(nl >= 1 && nl <= 6 * S.nlev + 1, "dss_c: nlayers must be in [1, 6*nlev+1] (size of the halo buffers)");
+  const size_t own = (size_t)n * nl * 16, all = (size_t)(n + S.nghost) * nl * 16;
+  double *d_f = nullptr, *d_o = nullptr;
+  CUDA_OK(cudaMalloc(&d_f, all * sizeof(double)));
+  CUDA_OK(cudaMalloc(&d_o, own * sizeof(double)));
+  CUDA_OK(cudaMemcpyAsync(d_f, *field, own * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  if (!S.peers.empty()) {
+    launch_halo_generic(d_f, S.d_send_idx, (int)S.hsend_idx.size(), nl, S.d_sendbuf, 0, S.stream);
+    NCCL_OK(ncclGroupStart());
+    for (const Peer &p : S.peers) {
+      NCCL_OK(ncclSend(S.d_sendbuf + (size_t)p.send_off * nl, (size_t)p.send_cnt * nl, ncclDouble, p.rank, S.comm, S.stream));
+      NCCL_OK(ncclRecv(S.d_recvbuf + (size_t)p.recv_off * nl, (size_t)p.recv_cnt * nl, ncclDouble, p.rank, S.comm, S.stream));
+    }
+    NCCL_OK(ncclGroupEnd());
+    launch_halo_generic(d_f, S.d_recv_idx, (int)S.hrecv_idx.size(), nl, S.d_recvbuf, 1, S.stream);
+    S.launches += 2;
+  }
+  launch_dss_generic(d_f, d_o, S.geo.dss_src, n, nl, S.stream);
+  S.launches += 1;
+  CUDA_OK(cudaMemcpyAsync(*field, d_o, own * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  cudaFree(d_f); cudaFree(d_o);
+}
+
 void sync_diagnostics_to_host_c(void)
 {
   if (!S.device_ready) return;

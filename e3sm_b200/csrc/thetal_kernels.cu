@@ -1594,6 +1594,39 @@ void launch_forcing(const StatePtrs &s, const double *fm, const double *fvtheta,
   forcing_kernel<<<nelem, 256, 0, st>>>(s, fm, fvtheta, fphi, geo, dt, nlev);
 }
 
+// dss_c: direct stiffness summation of an arbitrary field f[ie][layer][16] (edgeVpack / bndry_exchangeV / edgeVunpack
+// of edge_mod.F90:500-629,862-944 as a node sum): gather with the same table and order as the step's kernels
+__global__ void __launch_bounds__(256) dss_generic_kernel(const double *f, double *out, const int *dss_src, int nl)
+{
+  const int ie = blockIdx.x, p = threadIdx.x & 15;
+  const int *src = dss_src + ((size_t)ie * 16 + p) * 3;
+  const int s0 = src[0], s1 = src[1], s2 = src[2];
+  for (int l = threadIdx.x >> 4; l < nl; l += 16) {
+    double s = f[((size_t)ie * nl + l) * 16 + p];
+    if (s0 >= 0) s = s + f[((size_t)(s0 >> 4) * nl + l) * 16 + (s0 & 15)];
+    if (s1 >= 0) s = s + f[((size_t)(s1 >> 4) * nl + l) * 16 + (s1 & 15)];
+    if (s2 >= 0) s = s + f[((size_t)(s2 >> 4) * nl + l) * 16 + (s2 & 15)];
+    out[((size_t)ie * nl + l) * 16 + p] = s;
+  }
+}
+__global__ void __launch_bounds__(256) halo_generic_kernel(double *f, const int *idx, int nent, int nl, double *buf, int unpack)
+{
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)nent * nl) return;
+  const int ent = (int)(i / nl), l = (int)(i - (long)ent * nl), ep = idx[ent];
+  double *a = f + ((size_t)(ep >> 4) * nl + l) * 16 + (ep & 15);
+  if (unpack) *a = buf[i]; else buf[i] = *a;
+}
+void launch_dss_generic(const double *f, double *out, const int *dss_src, int nelem, int nl, cudaStream_t st)
+{
+  dss_generic_kernel<<<nelem, 256, 0, st>>>(f, out, dss_src, nl);
+}
+void launch_halo_generic(double *f, const int *idx, int nent, int nl, double *buf, int unpack, cudaStream_t st)
+{
+  const long n = (long)nent * nl;
+  if (n > 0) halo_generic_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(f, idx, nent, nl, buf, unpack);
+}
+
 // ps_v = hyai(1) ps0 + sum_k dp3d (vertremap_mod.F90:79-84) and its inverse on the reference levels,
 // dp3d(k) = (hyai(k+1)-hyai(k)) ps0 + (hybi(k+1)-hybi(k)) ps_v (prim_driver.cpp:31-57); one thread per column
 __global__ void ps_from_dp_kernel(const double *dp, double *ps, int nelem, int nlev, double ptop)

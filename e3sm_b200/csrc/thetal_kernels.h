@@ -100,6 +100,8 @@ void launch_forcing(const StatePtrs &s, const double *fm, const double *fvtheta,
                     double dt, int nelem, int nlev, cudaStream_t st);
 void launch_ps_from_dp(const double *dp, double *ps, int nelem, int nlev, double ptop, cudaStream_t st);
 void launch_dp_from_ps(double *dp, const double *ps, int nelem, int nlev, double ps0, cudaStream_t st);
+void launch_dss_generic(const double *f, double *out, const int *dss_src, int nelem, int nl, cudaStream_t st);
+void launch_halo_generic(double *f, const int *idx, int nent, int nl, double *buf, int unpack, cudaStream_t st);
 double launch_fp64_peak(cudaStream_t st);   // returns the flops the launch performs
 void launch_wbc(const StatePtrs &s, const Geo &geo, int nelem, int nlev, cudaStream_t st);
 

@@ -232,6 +232,13 @@ class ThetaLDycore:
         self.L.apply_cam_forcing_dynamics_c(_ci(nt), _cd(dt))
         self._check()
 
+    def dss(self, field):
+        """dss_c: node sums of field[nelem, nlayers, 16] in place (edgeVpack / bndry_exchangeV / edgeVunpack)."""
+        assert field.flags["C_CONTIGUOUS"] and field.dtype == np.float64 and field.shape[0] == self.nelem and field.shape[-1] == 16
+        self.L.dss_c(_pp(field), _ci(field.size // (self.nelem * 16)))
+        self._check()
+        return field
+
     def init_time_level(self, nm1, n0, np1, nstep=0, nstep0=0):
         """init_time_level_c with 1-BASED levels like the Fortran caller (prim_driver_mod.F90:196)."""
         self.L.init_time_level_c(_ci(nm1), _ci(n0), _ci(np1), _ci(nstep), _ci(nstep0))

@@ -89,6 +89,9 @@ void init_elements_states_strided_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f
  * (prim_driver.cpp:117-125 -> applyCAMforcing_dynamics, prim_advance_mod.F90:517-541, standalone variant). */
 void push_forcing_to_c(const double *fm, const double *fvtheta, const double *ft,
                        const double *fphi, const double *fq);
+/* addition: DSS of a caller's field(np,np,nlayers,nelemd) in place (node sums in the Fortran unpack order,
+ * edge_mod.F90:500-629,862-944; halos over NCCL when partitioned); nlayers <= 6*nlev+1 */
+void dss_c(thetal_f90ptr_out field, const int *nlayers);
 /* addition: applyCAMforcing_dynamics alone on time level *nt (0-based), for parity tests */
 void apply_cam_forcing_dynamics_c(const int *nt, const double *dt);
 /* nstep, nm1, n0, np1 are pure OUTPUTS (never read): the library advances its own TimeLevel, set by

@@ -56,7 +56,12 @@ def _rank_main(rank, world, port, cfg, over, nsteps, q):
         out = d.get_state()
         ex, by = d.halo_stats()
         diag = d.global_diagnostics(tl)
-        q.put((rank, {f: getattr(out, f)[:, tl].copy() for f in FIELDS}, ex, by, diag))
+        # dss_c of a field that depends only on the global element number: halos of a caller's field over NCCL
+        e0, e1 = part.local_range(rank)
+        gid = np.asarray(grid.gnum[e0:e1], dtype=np.float64)
+        fld = np.ascontiguousarray(np.sin(gid[:, None, None] * 0.37 + np.arange(3)[None, :, None] + 0.11 * np.arange(16)[None, None, :]))
+        dssf = d.dss(fld.copy())
+        q.put((rank, {f: getattr(out, f)[:, tl].copy() for f in FIELDS}, ex, by, diag, dssf))
         td.barrier()
         d.close()
     finally:
@@ -103,6 +108,10 @@ def test_partitioned_run_equals_single_gpu_bitwise(world, over):
         single = getattr(one, f)[:, tl]
         assert multi.shape == single.shape
         assert np.array_equal(multi, single), f"{f}: partitioned run differs from the single-GPU run"
+    from e3sm_b200.geometry import dss_numpy
+    gid = np.asarray(grid.gnum, dtype=np.float64)
+    fld = np.sin(gid[:, None, None] * 0.37 + np.arange(3)[None, :, None] + 0.11 * np.arange(16)[None, None, :])
+    assert np.array_equal(np.concatenate([r[5] for r in res], axis=0), dss_numpy(fld, grid.dss_src)), "dss_c across ranks"
     for r in res:
         assert r[2] > 0 and r[3] > 0          # every rank really exchanged halos
         # device diagnostics: order-independent sum + NCCL all-reduce of integers = the single-GPU bits

@@ -633,3 +633,18 @@ def test_one_step_on_the_real_ne30_sphere(cfg):
     dw = float(np.abs(sg.w_i[:, n0] - so.w_i[:, n0]).max())
     assert dw <= 1e-10 * max(1.0, float(np.abs(so.w_i[:, n0]).max())), dw
     d.close()
+
+
+def test_dss_c_of_a_user_field(case_c1):
+    """dss_c: node sums of an arbitrary field in the Fortran unpack order = the reference DSS of geometry.dss_numpy"""
+    from e3sm_b200.dycore import ThetaLDycore
+    from e3sm_b200.geometry import dss_numpy
+    p, grid, hv, st, phis, gradphis, refs = case_c1
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+    rng = np.random.default_rng(11)
+    for nl in (1, 7, 6 * hv.nlev + 1):
+        f = rng.standard_normal((grid.nelem, nl, 16))
+        want = dss_numpy(f, grid.dss_src)
+        got = d.dss(f.copy())
+        assert np.array_equal(got, want), nl
+    d.close()
