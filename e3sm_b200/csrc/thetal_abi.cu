@@ -1088,6 +1088,41 @@ void thetal_b200_global_diagnostics(const int *tl, double *out)
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);
 
+// Field extrema of time level *tl as prim_printstate reports them (prim_state_mod.F90:219-330): out[2f], out[2f+1] =
+// global min, max of f = u, v, w_i, theta, T, dz, dp3d (7 fields, 14 numbers), the same on every rank.
+void thetal_b200_field_extrema(const int *tl, double *out)
+{
+  REQUIRE(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_field_extrema: bad state/time level");
+  static unsigned long long *d_keys = nullptr;
+  if (!d_keys) d_keys = dalloc<unsigned long long>(2 * NEXTREMA);
+  unsigned long long init[2 * NEXTREMA], h[2 * NEXTREMA];
+  for (int f = 0; f < NEXTREMA; f++) { init[2 * f] = ~0ULL; init[2 * f + 1] = 0ULL; }
+  CUDA_OK(cudaMemcpyAsync(d_keys, init, sizeof init, cudaMemcpyHostToDevice, S.stream));
+  DiagArgs a;
+  a.st = S.tl[*tl]; a.geo = S.geo; a.prm = S.prm; a.part = nullptr; a.maxbits = nullptr; a.ps_minmax = nullptr;
+  launch_extrema(a, d_keys, S.stream); S.launches += 1;
+  CUDA_OK(cudaMemcpyAsync(h, d_keys, sizeof h, cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  if (S.nranks > 1) {       // min and max keys of all ranks: interleaved, so two strided reductions on the host copy
+    unsigned long long mins[NEXTREMA], maxs[NEXTREMA];
+    for (int f = 0; f < NEXTREMA; f++) { mins[f] = h[2 * f]; maxs[f] = h[2 * f + 1]; }
+    CUDA_OK(cudaMemcpyAsync(d_keys, mins, sizeof mins, cudaMemcpyHostToDevice, S.stream));
+    CUDA_OK(cudaMemcpyAsync(d_keys + NEXTREMA, maxs, sizeof maxs, cudaMemcpyHostToDevice, S.stream));
+    NCCL_OK(ncclGroupStart());
+    NCCL_OK(ncclAllReduce(d_keys, d_keys, NEXTREMA, ncclUint64, ncclMin, S.comm, S.stream));
+    NCCL_OK(ncclAllReduce(d_keys + NEXTREMA, d_keys + NEXTREMA, NEXTREMA, ncclUint64, ncclMax, S.comm, S.stream));
+    NCCL_OK(ncclGroupEnd());
+    CUDA_OK(cudaMemcpyAsync(mins, d_keys, sizeof mins, cudaMemcpyDeviceToHost, S.stream));
+    CUDA_OK(cudaMemcpyAsync(maxs, d_keys + NEXTREMA, sizeof maxs, cudaMemcpyDeviceToHost, S.stream));
+    CUDA_OK(cudaStreamSynchronize(S.stream));
+    for (int f = 0; f < NEXTREMA; f++) { h[2 * f] = mins[f]; h[2 * f + 1] = maxs[f]; }
+  }
+  for (int i = 0; i < 2 * NEXTREMA; i++) {
+    const unsigned long long k = h[i], b = (k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k;
+    memcpy(&out[i], &b, 8);
+  }
+}
+
 
 // ---------------------------------------------------------------- the step
 static bool tl_ok(int t) { return t >= 0 && t < NTL; }

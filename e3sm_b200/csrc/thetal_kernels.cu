@@ -1824,6 +1824,55 @@ __global__ void __launch_bounds__(256) diag_accumulate_kernel(const double *part
   }
 }
 
+// prim_printstate's field extrema (prim_state_mod.F90:219-330): min and max over the rank of u, v, w_i, theta =
+// vtheta_dp/dp3d, T = theta*exner, dz = -dphi/g and dp3d.  Order-preserving integer keys make atomicMin/atomicMax
+// (and an NCCL min/max of integers) exact for either sign.
+__device__ __forceinline__ unsigned long long ordered_key(double x)
+{
+  const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__global__ void __launch_bounds__(256) extrema_kernel(const DiagArgs A, unsigned long long *keys)
+{
+  __shared__ double smin[NEXTREMA][8], smax[NEXTREMA][8];
+  const int nlev = A.prm.nlev, ie = blockIdx.x, tid = threadIdx.x, p = tid & 15, ks = tid >> 4;
+  const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * (nlev + 1), ev = (size_t)ie * 32 * nlev;
+  double lo[NEXTREMA], hi[NEXTREMA];
+#pragma unroll
+  for (int f = 0; f < NEXTREMA; f++) { lo[f] = 1e300; hi[f] = -1e300; }
+  for (int k = ks; k < nlev; k += 16) {
+    const int q = k * 16 + p;
+    const double dp = A.st.dp[em + q], th = A.st.th[em + q];
+    const double dphi = A.st.phi[ei + q + 16] - A.st.phi[ei + q];
+    const double poe = div_fast(RGAS * th, -dphi);
+    const double exner = div_fast(eos_pnh(poe), poe), theta = div_fast(th, dp);
+    const double val[NEXTREMA] = {A.st.v[ev + k * 32 + p], A.st.v[ev + k * 32 + 16 + p], A.st.w[ei + q], theta,
+                                  theta * exner, -dphi / G_GRAV, dp};
+#pragma unroll
+    for (int f = 0; f < NEXTREMA; f++) { lo[f] = fmin(lo[f], val[f]); hi[f] = fmax(hi[f], val[f]); }
+  }
+  if (ks == 0) { const double wb = A.st.w[ei + (size_t)nlev * 16 + p]; lo[2] = fmin(lo[2], wb); hi[2] = fmax(hi[2], wb); }
+#pragma unroll
+  for (int f = 0; f < NEXTREMA; f++) {
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[f] = fmin(lo[f], __shfl_xor_sync(0xffffffffu, lo[f], o));
+      hi[f] = fmax(hi[f], __shfl_xor_sync(0xffffffffu, hi[f], o));
+    }
+    if ((tid & 31) == 0) { smin[f][tid >> 5] = lo[f]; smax[f][tid >> 5] = hi[f]; }
+  }
+  __syncthreads();
+  if (tid < NEXTREMA) {
+    double a = smin[tid][0], b = smax[tid][0];
+    for (int i = 1; i < 8; i++) { a = fmin(a, smin[tid][i]); b = fmax(b, smax[tid][i]); }
+    atomicMin(keys + 2 * tid, ordered_key(a));
+    atomicMax(keys + 2 * tid + 1, ordered_key(b));
+  }
+}
+void launch_extrema(const DiagArgs &A, unsigned long long *keys, cudaStream_t st)
+{
+  extrema_kernel<<<A.prm.nelem, 256, 0, st>>>(A, keys);
+}
+
 void launch_diag_elements(const DiagArgs &A, cudaStream_t st)
 {
   diag_element_kernel<<<A.prm.nelem, 256, 0, st>>>(A);

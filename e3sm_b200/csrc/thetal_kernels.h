@@ -71,6 +71,7 @@ struct RemapArgs {
 };
 
 constexpr int NDIAG = 4;    // ps, KE, PE, IE
+constexpr int NEXTREMA = 7; // u, v, w_i, theta, T, dz, dp3d
 struct DiagArgs {
   StatePtrs st;
   Geo geo;
@@ -92,6 +93,7 @@ void launch_halo_pack(const StatePtrs &t, const int *idx, int nent, int nk, int 
 void launch_halo_unpack(const StatePtrs &t, const int *idx, int nent, int nk, int wbot, int nlev,
                         const double *buf, cudaStream_t st);
 void launch_diag_elements(const DiagArgs &A, cudaStream_t st);
+void launch_extrema(const DiagArgs &A, unsigned long long *keys, cudaStream_t st);   // keys[2*f] = min, [2*f+1] = max
 void launch_diag_accumulate(const double *part, int nelem, const unsigned long long *maxbits,
                             unsigned long long *limbs, cudaStream_t st);
 void upload_hyai(const double *hyai, int nlev);

@@ -289,6 +289,13 @@ class ThetaLDycore:
         keys = ("ps_min", "ps_max", "ps_mean", "KE", "PE", "IE", "energy")
         return {k: float(out[i]) for i, k in enumerate(keys)}
 
+    def field_extrema(self, tl):
+        """prim_printstate's extrema (prim_state_mod.F90:219-330): {name: (min, max)} for u, v, w, theta, T, dz, dp3d."""
+        out = np.zeros(14)
+        self.L.thetal_b200_field_extrema(_ci(tl), c_void_p(out.ctypes.data))
+        self._check()
+        return {k: (float(out[2 * i]), float(out[2 * i + 1])) for i, k in enumerate(("u", "v", "w", "theta", "T", "dz", "dp3d"))}
+
     def halo_stats(self):
         ex, by = ctypes.c_long(0), ctypes.c_long(0)
         self.L.thetal_b200_halo_stats(byref(ex), byref(by))

@@ -89,6 +89,9 @@ void init_elements_states_strided_c(thetal_f90ptr v, thetal_f90ptr w_i, thetal_f
  * (prim_driver.cpp:117-125 -> applyCAMforcing_dynamics, prim_advance_mod.F90:517-541, standalone variant). */
 void push_forcing_to_c(const double *fm, const double *fvtheta, const double *ft,
                        const double *fphi, const double *fq);
+/* prim_printstate's field extrema of time level *tl (0-based), prim_state_mod.F90:219-330: out[2f], out[2f+1] = global
+ * min, max of f = u, v, w_i, theta, T, dz, dp3d (14 doubles); identical on every rank */
+void thetal_b200_field_extrema(const int *tl, double *out);
 /* addition: DSS of a caller's field(np,np,nlayers,nelemd) in place (node sums in the Fortran unpack order,
  * edge_mod.F90:500-629,862-944; halos over NCCL when partitioned); nlayers <= 6*nlev+1 */
 void dss_c(thetal_f90ptr_out field, const int *nlayers);

@@ -648,3 +648,26 @@ def test_dss_c_of_a_user_field(case_c1):
         got = d.dss(f.copy())
         assert np.array_equal(got, want), nl
     d.close()
+
+
+def test_field_extrema_match_numpy(case_c1, parity_state_c1):
+    """thetal_b200_field_extrema: the min/max lines of prim_printstate (prim_state_mod.F90:219-330)"""
+    from e3sm_b200.dycore import ThetaLDycore
+    from e3sm_b200.geometry import G, KAPPA, P0, RGAS
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    st = distinct_levels(parity_state_c1, phis, gradphis)
+    d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+    d.set_state(st)
+    tl = 2
+    ex = d.field_extrema(tl)
+    dp, th, phi = st.dp3d[:, tl], st.vtheta_dp[:, tl], st.phinh_i[:, tl]
+    dphi = phi[:, 1:] - phi[:, :-1]
+    poe = RGAS * th / (-dphi)
+    exner = (P0 * (poe / P0) ** (1.0 / (1.0 - KAPPA))) / poe
+    want = {"u": st.v[:, tl, :, 0], "v": st.v[:, tl, :, 1], "w": st.w_i[:, tl], "theta": th / dp, "T": th / dp * exner,
+            "dz": -dphi / G, "dp3d": dp}
+    for k, a in want.items():
+        lo, hi = ex[k]
+        assert abs(lo - a.min()) <= 1e-12 * max(1.0, abs(a.min())) and abs(hi - a.max()) <= 1e-12 * max(1.0, abs(a.max())), (k, ex[k], a.min(), a.max())
+    assert ex["u"][0] < 0 < ex["u"][1]            # both signs go through the ordered keys
+    d.close()
