@@ -85,7 +85,8 @@ struct Session {
   Geo geo{};
   Derived der{};
   RefStates ref{};
-  int *d_err = nullptr, *d_maxiter = nullptr;
+  int *d_err = nullptr, *d_maxiter = nullptr, *d_dirk_work = nullptr;
+  long dirk_launches = 0;
   unsigned long long *d_maxdelta = nullptr;
   double *d_diag_part = nullptr;            // [nelem][NDIAG] element integrals
   unsigned long long *d_diag_acc = nullptr; // [NDIAG] max bits, [2] ps min/max bits, [NDIAG*3] limbs
@@ -543,6 +544,7 @@ void init_functors_c(const int *allocate_buffer)
   S.ref.dp_ref = dalloc<double>((size_t)n * 16 * nlev);
   S.ref.phi_ref = dalloc<double>((size_t)n * 16 * (nlev + 1));
   for (int t = 0; t < NTL; t++) S.d_ps_v[t] = dalloc<double>((size_t)n * 16);
+  S.d_dirk_work = dalloc<int>(2);
   S.d_err = dalloc<int>(1); S.d_maxiter = dalloc<int>(1); S.d_maxdelta = dalloc<unsigned long long>(1);
   S.d_diag_part = dalloc<double>((size_t)S.prm.nelem * NDIAG); S.d_diag_acc = dalloc<unsigned long long>(NDIAG + 2 + NDIAG * thetal_reprosum::NLIMB);
   if (S.nu_scale_top.empty()) S.nu_scale_top.assign(nlev, 0.0);
@@ -700,6 +702,8 @@ void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2, b
   a.np1 = S.tl[np1]; a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.geo = S.geo; a.prm = S.prm;
   a.dt2 = dt2; a.alphadt_n0 = a_n0; a.alphadt_nm1 = a_nm1;
   a.err = S.d_err; a.max_iter = S.d_maxiter; a.max_deltaerr_bits = S.d_maxdelta;
+  a.work = S.d_dirk_work + (S.dirk_launches & 1); a.work_other = S.d_dirk_work + ((S.dirk_launches + 1) & 1);
+  S.dirk_launches++;
   { ProfScope ps(2); launch_dirk(a, S.stream); }
   S.launches += 1;
 }

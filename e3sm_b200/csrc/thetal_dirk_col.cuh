@@ -163,20 +163,24 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   const double *cth = st_th + p * SS, *cdp = st_dp + p * SS, *cw = st_w + p * SS, *cphi = st_phi + p * SS;
   const double *cv1 = st_v1 + p * SS, *cv2 = st_v2 + p * SS;       // this thread's column in the staging area
 
-  int ie = blockIdx.x;
+  // Elements beyond the first gridDim.x are handed out dynamically (an atomic counter per launch): elements differ in
+  // their Newton work, and a static stride leaves some CTAs with one element more than others.
+  __shared__ int s_next;
+  int ie = blockIdx.x, ie_next = nelem;
+  if (blockIdx.x == 0 && tid == 0) *A.work_other = 0;         // the counter of the previous launch, for the next one
   if (ie < nelem) { stage_state(A.np1, ie); prefetch_explicit(ie); }
   int bad = 0;
-  for (; ie < nelem; ie += gridDim.x) {
+  for (; ie < nelem; ie = ie_next) {
   double *gw = A.np1.w + (size_t)ie * 16 * nlevp, *gphi = A.np1.phi + (size_t)ie * 16 * nlevp;
   const double gp1 = A.geo.gradphis[(size_t)ie * 32 + p], gp2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
-  const int ie_next = ie + (int)gridDim.x;
-  if (tid == 0) sflag = 0;
-  if (ie_next < nelem) prefetch_explicit(ie_next);
+  if (tid == 0) { sflag = 0; s_next = (int)gridDim.x + atomicAdd(A.work, 1); }
 
   double w[ITEMS], dphi[ITEMS], rdpi[ITEMS], rth[ITEMS];
   double dp[ITEMS], w0[ITEMS], phi0[ITEMS], v1[ITEMS], v2[ITEMS];
   cp_async_wait_all();
   __syncthreads();
+  ie_next = s_next;
+  if (ie_next < nelem) prefetch_explicit(ie_next);
   // ---- the column slice, wmax (IM:168-170) ----
   double wmax = 0.0;
   const double dpm0 = cdp[km], v1m0 = cv1[km], v2m0 = cv2[km];   // level above the slice

@@ -37,6 +37,7 @@ struct DirkArgs {
   double dt2, alphadt_n0, alphadt_nm1;
   // optional: explicit terms of state(n0) / state(nm1) saved by the CAAR launches that evaluated those states
   const double *ew_n0 = nullptr, *ephi_n0 = nullptr, *ew_nm1 = nullptr, *ephi_nm1 = nullptr;
+  int *work = nullptr, *work_other = nullptr;   // element counter of this launch / of the previous one (reset here)
   int *err;
   int *max_iter;            // running max of itercount over elements (atomicMax)
   unsigned long long *max_deltaerr_bits;   // running max of deltaerr (as ordered bits)
