@@ -87,7 +87,7 @@ struct Session {
   RefStates ref{};
   int *d_err = nullptr, *d_maxiter = nullptr, *d_dirk_work = nullptr;
   long dirk_launches = 0;
-  unsigned long long *d_maxdelta = nullptr;
+  unsigned long long *d_maxdelta = nullptr, *d_extrema = nullptr;
   double *d_diag_part = nullptr;            // [nelem][NDIAG] element integrals
   unsigned long long *d_diag_acc = nullptr; // [NDIAG] max bits, [2] ps min/max bits, [NDIAG*3] limbs
   bool device_ready = false;
@@ -1097,8 +1097,8 @@ void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, c
 void thetal_b200_field_extrema(const int *tl, double *out)
 {
   REQUIRE(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_field_extrema: bad state/time level");
-  static unsigned long long *d_keys = nullptr;
-  if (!d_keys) d_keys = dalloc<unsigned long long>(2 * NEXTREMA);
+  if (!S.d_extrema) S.d_extrema = dalloc<unsigned long long>(2 * NEXTREMA);     // freed with the session
+  unsigned long long *d_keys = S.d_extrema;
   unsigned long long init[2 * NEXTREMA], h[2 * NEXTREMA];
   for (int f = 0; f < NEXTREMA; f++) { init[2 * f] = ~0ULL; init[2 * f + 1] = 0ULL; }
   CUDA_OK(cudaMemcpyAsync(d_keys, init, sizeof init, cudaMemcpyHostToDevice, S.stream));

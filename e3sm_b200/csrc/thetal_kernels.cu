@@ -1148,8 +1148,13 @@ void launch_dirk(const DirkArgs &A, cudaStream_t st)
       case 4: launch_dirk_col_t<4, 16>(A, st); break;
       case 5: launch_dirk_col_t<5, 16>(A, st); break;
       case 6: launch_dirk_col_t<6, 16>(A, st); break;
-      case 7: launch_dirk_col_t<7, 16>(A, st); break;
-      default: launch_dirk_col_t<8, 16>(A, st); break;
+      default: {      // 97..128 levels: a full warp per column (4 levels per lane, 512 threads) keeps the registers at 128
+        static const int wide = [] { const char *e = getenv("THETAL_B200_DIRK_TPC32"); return e ? atoi(e) : 1; }();
+        if (wide) launch_dirk_col_t<4, 32>(A, st);
+        else if (A.prm.nlev <= 112) launch_dirk_col_t<7, 16>(A, st);
+        else launch_dirk_col_t<8, 16>(A, st);
+        break;
+      }
     }
     return;
   }
