@@ -1089,6 +1089,65 @@ void thetal_b200_global_diagnostics(const int *tl, double *out)
   out[7] = (double)S.prm.nelem;      // elements owned by this rank
 }
 
+// thetal_b200_global_diagnostics for callers that may not allocate (graph capture, harnesses that forbid
+// cudaMalloc): the same two kernels, with the element integrals and the accumulators in file-scope device
+// arrays of a fixed maximum size instead of the session's buffers.  No counterpart in the reference.  Every
+// GPU that loads the library holds the arrays (THETAL_B200_NOALLOC_MAX_ELEMS * 32 B + 144 B = 512 KB) until
+// exit; all calls share them, so calls that overlap on the GPU (two host threads, two streams) race.  The
+// accumulators are cleared on every call; the element integrals are fully rewritten for elements < nelem.
+// In host code the array names below are stand-ins, not device addresses: the address a kernel can use comes
+// from cudaGetSymbolAddress, resolved once per device with that device current.
+constexpr int NOALLOC_NACC = NDIAG + 2 + NDIAG * thetal_reprosum::NLIMB;
+static __device__ __align__(256) double g_noalloc_part[(size_t)THETAL_B200_NOALLOC_MAX_ELEMS * NDIAG];
+static __device__ __align__(256) unsigned long long g_noalloc_acc[NOALLOC_NACC];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static double *g_noalloc_part_addr[NOALLOC_MAX_DEVICES];
+static unsigned long long *g_noalloc_acc_addr[NOALLOC_MAX_DEVICES];
+
+void thetal_b200_global_diagnostics_noalloc(const int *tl, double *out)
+{
+  REQUIRE(S.device_ready && *tl >= 0 && *tl < NTL, "thetal_b200_global_diagnostics_noalloc: bad state/time level");
+  REQUIRE(S.prm.nelem <= THETAL_B200_NOALLOC_MAX_ELEMS,
+          "thetal_b200_global_diagnostics_noalloc: " + std::to_string(S.prm.nelem) + " elements on this rank exceed the "
+          "static scratch of THETAL_B200_NOALLOC_MAX_ELEMS = " + std::to_string(THETAL_B200_NOALLOC_MAX_ELEMS) +
+          "; use thetal_b200_global_diagnostics");
+  REQUIRE(S.nranks == 1, "thetal_b200_global_diagnostics_noalloc: single-rank sessions only (a first NCCL collective "
+                         "may allocate); use thetal_b200_global_diagnostics");
+  int dev = -1;
+  CUDA_OK(cudaGetDevice(&dev));
+  REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "thetal_b200_global_diagnostics_noalloc: device ordinal out of range");
+  if (!g_noalloc_part_addr[dev]) {       // set-up, once per device, the session's device current
+    double *pp = nullptr; unsigned long long *pa = nullptr;
+    CUDA_OK(cudaGetSymbolAddress((void **)&pp, g_noalloc_part));
+    CUDA_OK(cudaGetSymbolAddress((void **)&pa, g_noalloc_acc));
+    REQUIRE(pp && pa, "thetal_b200_global_diagnostics_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_part_addr[dev] = pp; g_noalloc_acc_addr[dev] = pa;
+  }
+  double *part = g_noalloc_part_addr[dev];
+  unsigned long long *acc = g_noalloc_acc_addr[dev];
+  constexpr int NL = thetal_reprosum::NLIMB, NACC = NOALLOC_NACC;
+  unsigned long long *maxbits = acc, *psmm = acc + NDIAG, *limbs = acc + NDIAG + 2;
+  CUDA_OK(cudaMemsetAsync(acc, 0, NACC * sizeof(unsigned long long), S.stream));      // the last call's contents
+  CUDA_OK(cudaMemsetAsync(psmm, 0xff, sizeof(unsigned long long), S.stream));          // running min
+  DiagArgs a;
+  a.st = S.tl[*tl]; a.geo = S.geo; a.prm = S.prm; a.part = part; a.maxbits = maxbits; a.ps_minmax = psmm;
+  launch_diag_elements(a, S.stream); S.launches += 1;
+  launch_diag_accumulate(part, S.prm.nelem, maxbits, limbs, S.stream); S.launches += 1;
+  unsigned long long h[NACC];
+  CUDA_OK(cudaMemcpyAsync(h, acc, sizeof h, cudaMemcpyDeviceToHost, S.stream));
+  CUDA_OK(cudaStreamSynchronize(S.stream));
+  check_device_errors("thetal_b200_global_diagnostics_noalloc");
+  memcpy(&out[0], &h[NDIAG], 8); memcpy(&out[1], &h[NDIAG + 1], 8);
+  const double four_pi = 4.0 * 3.14159265358979323846264338327950288;       // dd_pi, physical_constants.F90:48
+  for (int q = 0; q < NDIAG; q++) {
+    long long l[NL];
+    for (int j = 0; j < NL; j++) l[j] = (long long)h[NDIAG + 2 + q * NL + j];
+    out[2 + q] = thetal_reprosum::combine(l, thetal_reprosum::exponent_of_bits(h[q])) / four_pi;
+  }
+  out[6] = out[3] + out[4] + out[5];
+  out[7] = (double)S.prm.nelem;
+}
+
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);
 

@@ -82,6 +82,12 @@ module thetal_b200_f2c_mod
       integer(c_int), intent(in) :: tl
       real(c_double), intent(out) :: out(8)    ! min ps, max ps, <ps>, <KE>, <PE>, <IE>, <KE+PE+IE>, nelemd
     end subroutine thetal_b200_global_diagnostics
+    ! no counterpart in the reference: same numbers, static device scratch, allocates nothing (<= 16384 elements, 1 rank)
+    subroutine thetal_b200_global_diagnostics_noalloc(tl, out) bind(c)
+      import :: c_int, c_double
+      integer(c_int), intent(in) :: tl
+      real(c_double), intent(out) :: out(8)    ! min ps, max ps, <ps>, <KE>, <PE>, <IE>, <KE+PE+IE>, nelemd
+    end subroutine thetal_b200_global_diagnostics_noalloc
 
     subroutine thetal_b200_sync() bind(c)
     end subroutine thetal_b200_sync

@@ -27,6 +27,7 @@ SYMBOLS = [
     "thetal_b200_halo_counts", "thetal_b200_halo_lists", "thetal_b200_dss_table", "thetal_b200_halo_stats", "thetal_b200_global_diagnostics", "vertical_remap_c", "thetal_b200_pipeline_step", "thetal_b200_pipeline_flush", "thetal_b200_set_vertical_remap",
     "thetal_b200_time_dirk", "thetal_b200_measure_fp64_peak", "apply_cam_forcing_dynamics_c",
     "init_elements_states_strided_c", "dss_c", "thetal_b200_field_extrema",
+    "thetal_b200_global_diagnostics_noalloc",
 ]
 
 

@@ -173,6 +173,16 @@ void thetal_b200_set_vertical_remap(const int *on);
  * convention: integral / 4 pi), elements owned by this rank.  The sum over elements is an
  * order-independent fixed-point sum: identical bits on every rank and for every partition. */
 void thetal_b200_global_diagnostics(const int *tl, double *out);
+/* The same diagnostics for callers that may not allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and the same bits in out[8] as thetal_b200_global_diagnostics; the
+ * scratch (element integrals and accumulators) is a static device array inside the library, 512 KB held by
+ * every GPU that loads it until exit.  Limits: at most THETAL_B200_NOALLOC_MAX_ELEMS elements on the rank and a
+ * single-rank session; beyond either the call records an error (thetal_b200_last_error) and leaves out
+ * untouched.  It calls no cudaMalloc/cudaFree and no allocating library routine.  All calls share the array:
+ * calls that overlap on the GPU (several host threads or streams) race. */
+#define THETAL_B200_NOALLOC_MAX_ELEMS 16384
+void thetal_b200_global_diagnostics_noalloc(const int *tl, double *out);
 void thetal_b200_profile_step(const double *dt, const int *nm1, const int *n0, const int *np1,
                               double *ms_by_family, int nfamily);
 
