@@ -75,6 +75,7 @@ struct Session {
   int remap_alg = 1;        // vert_remap_u_alg (PPM variants only, as HOMMEXX)
   int do_remap = 1;         // prim_run_subcycle_c remaps after rsplit steps (thetal_b200_set_vertical_remap)
   int fuse_combo = 1;       // THETAL_B200_FUSE_COMBO=0: separate combo_kernel launch for the tstep_type 9 combination
+  int fuse_dss = 1;         // THETAL_B200_FUSE_DSS=0: caar_dss_post_kernel between every CAAR stage and its DIRK solve
   int expl_cache = 1;       // THETAL_B200_EXPL_CACHE=0: the closing DIRK stage redoes the EOS of state(n0), state(nm1)
   int overlap = 1;          // halo of a DSS travels while the producer runs on the interior elements
   // device
@@ -165,6 +166,8 @@ void initialize_hommexx_session(void)
   CUDA_OK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
   if (getenv("THETAL_B200_EXPL_CACHE")) S.expl_cache = atoi(getenv("THETAL_B200_EXPL_CACHE"));
   if (getenv("THETAL_B200_FUSE_COMBO")) S.fuse_combo = atoi(getenv("THETAL_B200_FUSE_COMBO"));
+  if (getenv("THETAL_B200_FUSE_DSS")) S.fuse_dss = atoi(getenv("THETAL_B200_FUSE_DSS"));
+  if (getenv("THETAL_B200_DIRK") && atoi(getenv("THETAL_B200_DIRK")) != 1) S.fuse_dss = 0;   // only the column kernel has the DSS form
   CUDA_OK(cudaEventCreate(&S.ev0));
   CUDA_OK(cudaEventCreate(&S.ev1));
   if (S.nranks > 1) {
@@ -670,7 +673,7 @@ template <class F> void produce_and_exchange(const StatePtrs &t, int nk, int wbo
 // save_expl: 0 = no, 1 / 2 = keep the explicit stiff terms of state(n0) for the closing DIRK stage of this step in the
 // (otherwise idle) hyperviscosity scratch tensB: w/phi slots (1) or dp/th slots (2)
 void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3, int save_expl = 0,
-              int combo_b = -1, int combo_c = -1)
+              int combo_b = -1, int combo_c = -1, bool defer_dss = false)
 {
   Nvtx r("compute_andor_apply_rhs");
   CaarArgs a;
@@ -684,6 +687,7 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
     produce_and_exchange(S.tensA, S.nlev, 1, [&](const int *el, int n, cudaStream_t st) {
       a.elist = el; a.ecount = n; launch_caar_pre(a, st); });
   }
+  if (defer_dss) { S.launches += 1; return; }      // the DIRK launch that follows gathers from tensA itself
   DssArgs d;
   d.tens = S.tensA; d.out = S.tl[np1]; d.geo = S.geo; d.prm = S.prm; d.dt2 = dt2; d.scale1 = s1; d.scale3 = s3;
   d.do_limiter = (s3 != 0.0);
@@ -694,10 +698,13 @@ void run_caar(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1,
 }
 
 // cached: the explicit terms of state(n0) were saved by run_caar(..., save_expl = 1), those of state(nm1) by save_expl = 2
-void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2, bool cached = false)
+// dss_dt2 > 0: the preceding run_caar(..., defer_dss = true) left its pre-DSS result in tensA; its dt2, scale1 and scale3
+void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2, bool cached = false,
+              double dss_dt2 = 0.0, double dss_s1 = 0.0, double dss_s3 = 0.0)
 {
   Nvtx r("compute_stage_value_dirk");
   DirkArgs a;
+  if (dss_dt2 > 0.0) { a.tens = S.tensA; a.dss_dt2 = dss_dt2; a.dss_scale1 = dss_s1; a.dss_limiter = (dss_s3 != 0.0); }
   if (cached && S.expl_cache && S.prm.rsplit > 0) { a.ew_n0 = S.tensB.w; a.ephi_n0 = S.tensB.phi; a.ew_nm1 = S.tensB.dp; a.ephi_nm1 = S.tensB.th; }
   a.np1 = S.tl[np1]; a.n0 = S.tl[n0]; a.nm1 = S.tl[nm1]; a.geo = S.geo; a.prm = S.prm;
   a.dt2 = dt2; a.alphadt_n0 = a_n0; a.alphadt_nm1 = a_nm1;
@@ -706,6 +713,21 @@ void run_dirk(int nm1, double a_nm1, int n0, double a_n0, int np1, double dt2, b
   S.dirk_launches++;
   { ProfScope ps(2); launch_dirk(a, S.stream); }
   S.launches += 1;
+}
+
+// One IMEX stage whose DIRK solve works on the time level the CAAR stage has just produced (PA:283-311, 339-361):
+// compute_andor_apply_rhs(np1, nm1, n0, dt2, ...) then compute_stage_value_dirk(d_nm1, a_nm1, d_n0, a_n0, np1, d_dt2).
+// With fuse_dss the DSS between the two is done by the DIRK kernel (dirk_col_kernel<.., DSS = true>).
+void run_stage(int np1, int nm1, int n0, double dt2, double eta_ave_w, double s1, double s2, double s3, int save_expl,
+               int d_nm1, double a_nm1, int d_n0, double a_n0, double d_dt2)
+{
+  if (S.fuse_dss && dt2 > 0.0) {
+    run_caar(np1, nm1, n0, dt2, eta_ave_w, s1, s2, s3, save_expl, -1, -1, true);
+    run_dirk(d_nm1, a_nm1, d_n0, a_n0, np1, d_dt2, false, dt2, s1, s3);
+  } else {
+    run_caar(np1, nm1, n0, dt2, eta_ave_w, s1, s2, s3, save_expl);
+    run_dirk(d_nm1, a_nm1, d_n0, a_n0, np1, d_dt2);
+  }
 }
 
 void run_hypervis(int nt, double dt2, double eta_ave_w)
@@ -785,21 +807,21 @@ void run_prim_advance_exp(double dt, int nm1, int n0, int np1)
     case 7: {
       const double a1 = 0.0, a2 = 1 - a1;
       double dt2 = dt / 4;
-      run_caar(np1, n0, n0, dt2, 0.0, 1, 0, 1);  run_dirk(nm1, 0.0, n0, a1 * dt2, np1, a2 * dt2);
+      run_stage(np1, n0, n0, dt2, 0.0, 1, 0, 1, 0,  nm1, 0.0, n0, a1 * dt2, a2 * dt2);
       dt2 = dt / 6;
-      run_caar(nm1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt2, nm1, a2 * dt2);
+      run_stage(nm1, n0, np1, dt2, 0.0, 1, 0, 1, 0, nm1, 0.0, n0, a1 * dt2, a2 * dt2);
       dt2 = 3 * dt / 8;
-      run_caar(np1, n0, nm1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt2, np1, a2 * dt2);
+      run_stage(np1, n0, nm1, dt2, 0.0, 1, 0, 1, 0, nm1, 0.0, n0, a1 * dt2, a2 * dt2);
       dt2 = dt / 2;
-      run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt2, np1, a2 * dt2);
-      run_caar(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, a1 * dt, np1, a2 * dt);
+      run_stage(np1, n0, np1, dt2, 0.0, 1, 0, 1, 0, nm1, 0.0, n0, a1 * dt2, a2 * dt2);
+      run_stage(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 0, 1, 0, nm1, 0.0, n0, a1 * dt, a2 * dt);
       break;
     }
     case 9: {
-      run_caar(nm1, n0, n0, dt / 5, eta_ave_w / 4, 1, 0, 1, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt / 5);
-      run_caar(np1, n0, nm1, dt / 5, 0.0, 1, 0, 1, 2);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 5);
-      run_caar(np1, n0, np1, dt / 3, 0.0, 1, 0, 1);           run_dirk(nm1, 0.0, n0, 0.0, np1, dt / 3);
-      run_caar(np1, n0, np1, 2 * dt / 3, 0.0, 1, 0, 1);       run_dirk(nm1, 0.0, n0, 0.0, np1, 2 * dt / 3);
+      run_stage(nm1, n0, n0, dt / 5, eta_ave_w / 4, 1, 0, 1, 1,  nm1, 0.0, n0, 0.0, dt / 5);
+      run_stage(np1, n0, nm1, dt / 5, 0.0, 1, 0, 1, 2,           nm1, 0.0, n0, 0.0, dt / 5);
+      run_stage(np1, n0, np1, dt / 3, 0.0, 1, 0, 1, 0,           nm1, 0.0, n0, 0.0, dt / 3);
+      run_stage(np1, n0, np1, 2 * dt / 3, 0.0, 1, 0, 1, 0,       nm1, 0.0, n0, 0.0, 2 * dt / 3);
       if (S.fuse_combo) run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1, 0, nm1, n0);
       else { run_caar(np1, nm1, np1, 3 * dt / 4, 3 * eta_ave_w / 4, 1, 0, 1); run_combo(9, np1, nm1, n0); }
       const double a1 = 5 * dt / 18, a2 = dt / 36, a3 = 8 * dt / 18;
@@ -808,13 +830,13 @@ void run_prim_advance_exp(double dt, int nm1, int n0, int np1)
     }
     case 10: {
       double dt2 = dt / 4;
-      run_caar(nm1, n0, n0, dt2, 0.0, 1, 0, 1, 1);  run_dirk(nm1, 0.0, n0, 0.0, nm1, dt2);
+      run_stage(nm1, n0, n0, dt2, 0.0, 1, 0, 1, 1, nm1, 0.0, n0, 0.0, dt2);
       dt2 = dt / 6;
-      run_caar(np1, n0, nm1, dt2, 0.0, 1, 0, 1, 2); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      run_stage(np1, n0, nm1, dt2, 0.0, 1, 0, 1, 2, nm1, 0.0, n0, 0.0, dt2);
       dt2 = 3 * dt / 8;
-      run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      run_stage(np1, n0, np1, dt2, 0.0, 1, 0, 1, 0, nm1, 0.0, n0, 0.0, dt2);
       dt2 = dt / 2;
-      run_caar(np1, n0, np1, dt2, 0.0, 1, 0, 1); run_dirk(nm1, 0.0, n0, 0.0, np1, dt2);
+      run_stage(np1, n0, np1, dt2, 0.0, 1, 0, 1, 0, nm1, 0.0, n0, 0.0, dt2);
       run_caar(np1, n0, np1, dt, eta_ave_w * 1.0, 1, 0, 1);
       const double a1 = .24362, a2 = .34184, a3 = 1 - (a1 + a2);
       run_dirk(nm1, a2 * dt, n0, a1 * dt, np1, a3 * dt, true);

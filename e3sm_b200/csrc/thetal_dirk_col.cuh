@@ -80,6 +80,26 @@ __device__ __forceinline__ void eos_level(double rth, double dphi, double &pnh, 
   c = pnh * r;
 }
 
+// The same EOS after a Newton update that moved dphi by a small relative amount: with rth fixed,
+// pnh_new = pnh_old (dphi_old/dphi_new)^gamma, and (1 + e)^gamma is its binomial series in e = dphi_old/dphi_new - 1.
+// For |e| < 2^-4 the terms beyond degree 11 sum to less than 5e-18: the result differs from the full evaluation by
+// rounding only.  Thirteen FMAs instead of the ~65 of pow_pos.
+#ifndef DIRK_EOS_SERIES
+#define DIRK_EOS_SERIES 1
+#endif
+constexpr double EOS_SERIES_MAX = 0.0625;
+__device__ __forceinline__ void eos_level_small_step(double e, double r, double &pnh, double &c)
+{
+  constexpr double G1 = 1.0 / (1.0 - KAPPA), G2 = G1 * (G1 - 1) / 2, G3 = G2 * (G1 - 2) / 3, G4 = G3 * (G1 - 3) / 4,
+                   G5 = G4 * (G1 - 4) / 5, G6 = G5 * (G1 - 5) / 6, G7 = G6 * (G1 - 6) / 7, G8 = G7 * (G1 - 7) / 8,
+                   G9 = G8 * (G1 - 8) / 9, G10 = G9 * (G1 - 9) / 10, G11 = G10 * (G1 - 10) / 11;
+  double s = G11;
+  s = fma(s, e, G10); s = fma(s, e, G9); s = fma(s, e, G8); s = fma(s, e, G7); s = fma(s, e, G6);
+  s = fma(s, e, G5); s = fma(s, e, G4); s = fma(s, e, G3); s = fma(s, e, G2); s = fma(s, e, G1);
+  pnh = fma(pnh * e, s, pnh);
+  c = pnh * r;
+}
+
 template <int ITEMS, int TPC>
 struct DirkColCfg {
   static constexpr int NT = 16 * TPC;
@@ -101,7 +121,40 @@ __device__ __forceinline__ void cp_async8(double *dst, const double *src)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <int ITEMS, int TPC>
+// slow path of limiter_dp3d_k (PA:1859-1897) for one column held in the staging area (unit stride over the levels);
+// the same arithmetic as limiter_columns, which works on the finished state in global memory
+__device__ void limiter_column_staged(double *dp, double *th, int nlev, double spheremp, double dp3d_thresh)
+{
+  double mn = dp[0] - dp3d_thresh * c_dp0[0];
+  for (int k = 1; k < nlev; k++) mn = fmin(mn, dp[k] - dp3d_thresh * c_dp0[k]);
+  for (int k = 0; k < nlev; k++) th[k] = th[k] / dp[k];
+  if (mn < 0) {
+    double mass = 0, mass_new = 0;
+    for (int k = 0; k < nlev; k++) mass = mass + (dp[k] - dp3d_thresh * c_dp0[k]) * spheremp;
+    const double sgn = (mass < 0) ? -1.0 : 1.0;
+    for (int k = 0; k < nlev; k++) {
+      double Q = (dp[k] - dp3d_thresh * c_dp0[k]) * spheremp;
+      if (mass < 0) Q = -Q;
+      if (!(Q < 0)) mass_new = mass_new + Q;
+    }
+    for (int k = 0; k < nlev; k++) {
+      double Q = (dp[k] - dp3d_thresh * c_dp0[k]) * spheremp;
+      if (mass < 0) Q = -Q;
+      if (Q < 0) Q = 0;
+      if (mass_new > 0) Q = Q * (fabs(mass) / mass_new);
+      if (sgn < 0) Q = -Q;
+      dp[k] = Q / spheremp + dp3d_thresh * c_dp0[k];
+    }
+  }
+  for (int k = 0; k < nlev; k++) th[k] = th[k] * dp[k];
+}
+
+// DSS = true: the element's columns are staged from the pre-DSS buffer A.tens of the CAAR stage before this solve, and
+// the kernel finishes that stage itself (node sum over the neighbours, x rspheremp, surface fix-up, limiter_dp3d_k:
+// what caar_dss_post_kernel does) in the staging area before the Newton iteration starts; it then writes all six
+// prognostics of np1.  One pass over the state per stage instead of two (A.tens is read-only here, np1 is only
+// written by the CTA that owns the element, so there is no ordering between elements).
+template <int ITEMS, int TPC, bool DSS = false>
 __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk_col_kernel(const DirkArgs A)
 {
   constexpr int NT = 16 * TPC, NW = NT / 32, M = ITEMS;
@@ -168,7 +221,8 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   __shared__ int s_next;
   int ie = blockIdx.x, ie_next = nelem;
   if (blockIdx.x == 0 && tid == 0) *A.work_other = 0;         // the counter of the previous launch, for the next one
-  if (ie < nelem) { stage_state(A.np1, ie); prefetch_explicit(ie); }
+  const StatePtrs &SRC = DSS ? A.tens : A.np1;
+  if (ie < nelem) { stage_state(SRC, ie); prefetch_explicit(ie); }
   int bad = 0;
   for (; ie < nelem; ie = ie_next) {
   double *gw = A.np1.w + (size_t)ie * 16 * nlevp, *gphi = A.np1.phi + (size_t)ie * 16 * nlevp;
@@ -181,6 +235,68 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   __syncthreads();
   ie_next = s_next;
   if (ie_next < nelem) prefetch_explicit(ie_next);
+  if constexpr (DSS) {
+    // ---- DSS and post-processing of the CAAR stage (PA:1741-1772, 1812-1931), [level][point] over the threads ----
+    const int pt = tid & 15;
+    const int *src = A.geo.dss_src + ((size_t)ie * 16 + pt) * 3;
+    const int s0 = src[0], s1 = src[1], s2 = src[2];
+    const double rs = A.geo.rspheremp[(size_t)ie * 16 + pt];
+    const size_t ev = 2 * (size_t)n16, em = (size_t)n16, ei = 16 * (size_t)nlevp;
+    double *ov = A.np1.v + (size_t)ie * ev, *odp = A.np1.dp + (size_t)ie * em, *oth = A.np1.th + (size_t)ie * em;
+    int lim_dp = 0, lim_th = 0;
+    for (int k = tid >> 4; k < nlev; k += NT / 16) {
+      const int o = pt * SS + k;
+      const size_t offv = (size_t)k * 32, offm = (size_t)k * 16;
+      const double v1s = dss_sum(A.tens.v, ev, offv, st_v1[o], s0, s1, s2);
+      const double v2s = dss_sum(A.tens.v, ev, offv + 16, st_v2[o], s0, s1, s2);
+      const double dps = dss_sum(A.tens.dp, em, offm, st_dp[o], s0, s1, s2);
+      const double ths = dss_sum(A.tens.th, em, offm, st_th[o], s0, s1, s2);
+      const double ws = dss_sum(A.tens.w, ei, offm, st_w[o], s0, s1, s2);
+      const double phs = dss_sum(A.tens.phi, ei, offm, st_phi[o], s0, s1, s2);
+      double v1 = rs * v1s, v2 = rs * v2s;
+      const double dpk = rs * dps, thk = rs * ths;
+      st_dp[o] = dpk; st_th[o] = thk; st_w[o] = rs * ws; st_phi[o] = rs * phs;
+      if (k == nlev - 1) {                                                            // PA:1751-1772
+        const size_t ob = (size_t)nlev * 16;
+        double wb = rs * dss_sum(A.tens.w, ei, ob, st_w[o + 1], s0, s1, s2);
+        const double g1 = A.geo.gradphis[(size_t)ie * 32 + pt], g2 = A.geo.gradphis[(size_t)ie * 32 + 16 + pt];
+        const double dpnh = 1 + (((v1 * g1 + v2 * g2) / G_GRAV - wb) / (G_GRAV + (g1 * g1 + g2 * g2) / (2 * G_GRAV))) / A.dss_dt2;
+        wb = wb + A.dss_scale1 * A.dss_dt2 * G_GRAV * (dpnh - 1);
+        v1 = v1 - A.dss_scale1 * A.dss_dt2 * (dpnh - 1) * g1 / 2;
+        v2 = v2 - A.dss_scale1 * A.dss_dt2 * (dpnh - 1) * g2 / 2;
+        st_w[o + 1] = wb;
+        A.np1.w[(size_t)ie * ei + ob + pt] = wb;
+        st_phi[o + 1] = A.np1.phi[(size_t)ie * ei + ob + pt];      // phinh_i(nlevp) = phis: every time level holds it
+      }
+      st_v1[o] = v1; st_v2[o] = v2;
+      ov[offv + pt] = v1; ov[offv + 16 + pt] = v2;
+      if (dpk < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
+      if (thk - A.prm.vtheta_thresh * dpk < 0) lim_th = 1;
+    }
+    if (A.dss_limiter) {                    // limiter_dp3d_k: rare; block-uniform decisions
+      lim_dp = __syncthreads_or(lim_dp);
+      if (lim_dp) {
+        if (tid < 16) limiter_column_staged(st_dp + tid * SS, st_th + tid * SS, nlev, A.geo.spheremp[(size_t)ie * 16 + tid],
+                                            A.prm.dp3d_thresh);
+        __syncthreads();
+        lim_th = 0;
+        for (int k = tid >> 4; k < nlev; k += NT / 16)
+          if (st_th[pt * SS + k] - A.prm.vtheta_thresh * st_dp[pt * SS + k] < 0) lim_th = 1;
+      }
+      lim_th = __syncthreads_or(lim_th);
+      if (lim_th) {                                                                   // PA:1903-1925
+        for (int k = tid >> 4; k < nlev; k += NT / 16) {
+          const int o = pt * SS + k;
+          if (st_th[o] - A.prm.vtheta_thresh * st_dp[o] < 0) st_th[o] = A.prm.vtheta_thresh * st_dp[o];
+        }
+      }
+    }
+    __syncthreads();
+    for (int k = tid >> 4; k < nlev; k += NT / 16) {
+      const int o = pt * SS + k;
+      odp[(size_t)k * 16 + pt] = st_dp[o]; oth[(size_t)k * 16 + pt] = st_th[o];
+    }
+  }
   // ---- the column slice, wmax (IM:168-170) ----
   double wmax = 0.0;
   const double dpm0 = cdp[km], v1m0 = cv1[km], v2m0 = cv2[km];   // level above the slice
@@ -264,7 +380,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   // the staging area is consumed: fetch the next element of this CTA behind the Newton iterations
   if (ie_next < nelem) {
     if (expl) __syncthreads();
-    stage_state(A.np1, ie_next);
+    stage_state(SRC, ie_next);
   }
   // ---- wphis(np1) term (IM:208-211) ----
   {
@@ -280,6 +396,8 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   }
   // ---- hydrostatic initial guess phi_from_eos (EOS:286-302, IM:228-230) ----
   // running sums as (sum inside the lane) + (sum over the lanes above/below): the guess only starts Newton
+  double pnh[ITEMS], cc[ITEMS];
+  bool guess_kept;               // the hydrostatic guess was not clamped (IM:254-260 not taken)
   {
     double acc = 0.0, pin[ITEMS];
 #pragma unroll
@@ -292,6 +410,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       const double pmid = (pn + pi_k) / 2;
       const double t = div_p0(rth[i] * thetal_pow::pow_pos(div_p0(pmid), C_KM1));
       term[i] = (k0 + i < nlev) ? t : 0.0;
+      pnh[i] = pmid;
     }
     // phi_k = phis + sum_{k' >= k} term_k'
     double suf[ITEMS];
@@ -318,6 +437,7 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     }
     if (nsafe) sflag = 1;
     __syncthreads();
+    guess_kept = !sflag;
     if (sflag) {                                                                    // IM:254-260 (rare, whole element)
       acc = 0.0;
 #pragma unroll
@@ -333,11 +453,24 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       s_phi0[i * NT] = phi0[i];
     }
   }
-  double pnh[ITEMS], cc[ITEMS];
+#if DIRK_EOS_SERIES
+  if (guess_kept) {
+    // IM:261 at the hydrostatic guess: dphi was built so that the EOS returns the hydrostatic mid-level pressure
+    // (EOS:286-302 inverts EOS:175-183), so pnh = pmid up to the rounding of the interface sums (~1e-14); the Newton
+    // iteration does not depend on where it starts
 #pragma unroll
-  for (int i = 0; i < ITEMS; i++) {
-    if (k0 + i < nlev && dphi[i] > 0) bad = 1;
-    eos_level(rth[i], dphi[i], pnh[i], cc[i]);                                      // IM:261
+    for (int i = 0; i < ITEMS; i++) {
+      if (k0 + i < nlev && dphi[i] > 0) bad = 1;
+      cc[i] = pnh[i] * rcp_fast(dphi[i]);
+    }
+  } else
+#endif
+  {
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      if (k0 + i < nlev && dphi[i] > 0) bad = 1;
+      eos_level(rth[i], dphi[i], pnh[i], cc[i]);                                    // IM:261
+    }
   }
 
   // ---- Newton iteration (IM:268-336) ----
@@ -435,6 +568,11 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     if (j == TPC - 1) { x_next = 0.0; w_next = 0.0; }
     int anypos = 0;
     double xmax = 0.0;
+#if DIRK_EOS_SERIES
+    double dold[ITEMS];          // the dphi that pnh and cc were evaluated at
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) dold[i] = dphi[i];
+#endif
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
       const bool inlane = (i + 1 < ITEMS);
@@ -486,10 +624,26 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     deltaerr = div_fast(xmax, wmax);                                                // IM:330
     itercount++;
     if (deltaerr < 1.0e-11) break;                                                  // IM:335
+#if DIRK_EOS_SERIES
+    double rr[ITEMS], ee[ITEMS], emax = 0.0;
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
       if (k0 + i < nlev && dphi[i] > 0) bad = 1;
-      eos_level(rth[i], dphi[i], pnh[i], cc[i]);                                    // IM:324
+      rr[i] = rcp_fast(dphi[i]);
+      ee[i] = (dold[i] - dphi[i]) * rr[i];
+      emax = fmax(emax, fabs(ee[i]));
+    }
+    if (__all_sync(FULLMASK, emax < EOS_SERIES_MAX)) {
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) eos_level_small_step(ee[i], rr[i], pnh[i], cc[i]);
+    } else
+#endif
+    {
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) {
+        if (k0 + i < nlev && dphi[i] > 0) bad = 1;
+        eos_level(rth[i], dphi[i], pnh[i], cc[i]);                                  // IM:324
+      }
     }
   }
   // ---- phi update (IM:339) and write back ----
@@ -510,22 +664,22 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
 }
 
-template <int ITEMS, int TPC>
+template <int ITEMS, int TPC, bool DSS = false>
 static void launch_dirk_col_t(const DirkArgs &A, cudaStream_t st)
 {
   using Cfg = DirkColCfg<ITEMS, TPC>;
   static int grid_cap = 0;
   if (!grid_cap) {
-    cudaFuncSetAttribute(dirk_col_kernel<ITEMS, TPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    cudaFuncSetAttribute(dirk_col_kernel<ITEMS, TPC, DSS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     int dev = 0, nsm = 148, per_sm = 1;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dirk_col_kernel<ITEMS, TPC>, Cfg::NT, Cfg::smem_bytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dirk_col_kernel<ITEMS, TPC, DSS>, Cfg::NT, Cfg::smem_bytes);
     grid_cap = nsm * (per_sm > 0 ? per_sm : 1);      // persistent: every CTA resident, elements strided over them
   }
   static const int grid_env = [] { const char *e = getenv("THETAL_B200_DIRK_GRID"); return e ? atoi(e) : -1; }();
   int grid = A.prm.nelem < grid_cap ? A.prm.nelem : grid_cap;
   if (grid_env == 0) grid = A.prm.nelem;                       // tuning: one element per CTA
   else if (grid_env > 0 && grid_env < A.prm.nelem) grid = grid_env;
-  dirk_col_kernel<ITEMS, TPC><<<grid, Cfg::NT, Cfg::smem_bytes, st>>>(A);
+  dirk_col_kernel<ITEMS, TPC, DSS><<<grid, Cfg::NT, Cfg::smem_bytes, st>>>(A);
 }

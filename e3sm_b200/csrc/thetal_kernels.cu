@@ -531,9 +531,15 @@ __device__ __forceinline__ double dss_sum(const double *f, size_t estride, size_
                                           int s0, int s1, int s2)
 {
   double s = own;
+#ifndef DSS_NO_LDG
+  if (s0 >= 0) s = s + __ldg(f + (size_t)(s0 >> 4) * estride + off + (s0 & 15));
+  if (s1 >= 0) s = s + __ldg(f + (size_t)(s1 >> 4) * estride + off + (s1 & 15));
+  if (s2 >= 0) s = s + __ldg(f + (size_t)(s2 >> 4) * estride + off + (s2 & 15));
+#else
   if (s0 >= 0) s = s + f[(size_t)(s0 >> 4) * estride + off + (s0 & 15)];
   if (s1 >= 0) s = s + f[(size_t)(s1 >> 4) * estride + off + (s1 & 15)];
   if (s2 >= 0) s = s + f[(size_t)(s2 >> 4) * estride + off + (s2 & 15)];
+#endif
   return s;
 }
 
@@ -569,6 +575,18 @@ __device__ void limiter_columns(const StatePtrs &out, int ie, int nlev, int p, d
 
 
 constexpr int DSS_THREADS = 256;
+#ifndef DSS_MINB
+#define DSS_MINB 4
+#endif
+#ifndef DSS_UNROLL
+#define DSS_UNROLL 1
+#endif
+constexpr int DSS_UNROLL_N = DSS_UNROLL;
+#ifndef DSS_NO_LDG
+#define DSS_OWN(ptr) __ldg(&(ptr))
+#else
+#define DSS_OWN(ptr) (ptr)
+#endif
 
 // tstep_type 9 closing combination (PA:313-326): a(np1) += (b(nm1) - c(n0))/4 for one element, then limiter_dp3d_k.
 // Called by all DSS_THREADS threads of the CTA that owns element ie.
@@ -616,7 +634,7 @@ __device__ __forceinline__ void combo9_element(const StatePtrs &a, const StatePt
   }
 }
 
-__global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const DssArgs A)
+__global__ void __launch_bounds__(DSS_THREADS, DSS_MINB) caar_dss_post_kernel(const DssArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1;
   const int ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x;
@@ -635,14 +653,15 @@ __global__ void __launch_bounds__(DSS_THREADS, 4) caar_dss_post_kernel(const Dss
     if (tid == 4) prefetch_l2(A.tens.phi + ie * ei, (unsigned)(ei * 8));
   }
 
+#pragma unroll DSS_UNROLL_N
   for (int k = kslot; k < nlev; k += KS) {
     const size_t ov = (size_t)k * 32, om = (size_t)k * 16;
-    const double v1s = dss_sum(A.tens.v, ev, ov, A.tens.v[ie * ev + ov + p], s0, s1, s2);
-    const double v2s = dss_sum(A.tens.v, ev, ov + 16, A.tens.v[ie * ev + ov + 16 + p], s0, s1, s2);
-    const double dps = dss_sum(A.tens.dp, em, om, A.tens.dp[ie * em + om + p], s0, s1, s2);
-    const double ths = dss_sum(A.tens.th, em, om, A.tens.th[ie * em + om + p], s0, s1, s2);
-    const double ws = dss_sum(A.tens.w, ei, om, A.tens.w[ie * ei + om + p], s0, s1, s2);
-    const double phs = dss_sum(A.tens.phi, ei, om, A.tens.phi[ie * ei + om + p], s0, s1, s2);
+    const double v1s = dss_sum(A.tens.v, ev, ov, DSS_OWN(A.tens.v[ie * ev + ov + p]), s0, s1, s2);
+    const double v2s = dss_sum(A.tens.v, ev, ov + 16, DSS_OWN(A.tens.v[ie * ev + ov + 16 + p]), s0, s1, s2);
+    const double dps = dss_sum(A.tens.dp, em, om, DSS_OWN(A.tens.dp[ie * em + om + p]), s0, s1, s2);
+    const double ths = dss_sum(A.tens.th, em, om, DSS_OWN(A.tens.th[ie * em + om + p]), s0, s1, s2);
+    const double ws = dss_sum(A.tens.w, ei, om, DSS_OWN(A.tens.w[ie * ei + om + p]), s0, s1, s2);
+    const double phs = dss_sum(A.tens.phi, ei, om, DSS_OWN(A.tens.phi[ie * ei + om + p]), s0, s1, s2);
     double v1 = rs * v1s, v2 = rs * v2s;
     const double dp = rs * dps, th = rs * ths;
     A.out.dp[ie * em + om + p] = dp;
@@ -1141,6 +1160,17 @@ namespace thetal {
 void launch_dirk(const DirkArgs &A, cudaStream_t st)
 {
   static const int variant = [] { const char *e = getenv("THETAL_B200_DIRK"); return e ? atoi(e) : 1; }();
+  if (variant == 1 && A.tens.v) {     // the same solve behind the DSS of the preceding CAAR stage (one pass over the state)
+    switch ((A.prm.nlev + 15) / 16) {
+      case 0: case 1: case 2: launch_dirk_col_t<2, 16, true>(A, st); break;
+      case 3: launch_dirk_col_t<3, 16, true>(A, st); break;
+      case 4: launch_dirk_col_t<4, 16, true>(A, st); break;
+      case 5: launch_dirk_col_t<5, 16, true>(A, st); break;
+      case 6: launch_dirk_col_t<6, 16, true>(A, st); break;
+      default: launch_dirk_col_t<4, 32, true>(A, st); break;
+    }
+    return;
+  }
   if (variant == 1) {       // column-parallel solve (half-warp per column, partition + cyclic reduction)
     switch ((A.prm.nlev + 15) / 16) {
       case 0: case 1: case 2: launch_dirk_col_t<2, 16>(A, st); break;
@@ -1433,7 +1463,7 @@ __global__ void __launch_bounds__(HV_THREADS, HV_MINB) hv_laplace2_kernel(const 
 }
 
 // pass 3 (PA:674-758, 767-774): DSS(tin) * dt * rspheremp added to the state
-__global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A)
+__global__ void __launch_bounds__(HV_THREADS, DSS_MINB) hv_update_kernel(const HvArgs A)
 {
   const int nlev = A.prm.nlev, nlevp = nlev + 1, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
@@ -1443,15 +1473,16 @@ __global__ void __launch_bounds__(HV_THREADS, 4) hv_update_kernel(const HvArgs A
   const double rs = A.geo.rspheremp[(size_t)ie * 16 + p], dt = A.dt;
   const size_t sm_ = 16 * (size_t)nlev, si = 16 * (size_t)nlevp, sv = 32 * (size_t)nlev;
   const size_t em = ie * sm_, ei = ie * si, ev = ie * sv;
+#pragma unroll DSS_UNROLL_N
   for (int k = kslot; k < nlev; k += KS) {
     const int q = k * 16 + p;
     const size_t om = (size_t)k * 16, ov = (size_t)k * 32;
-    const double tdp = dt * dss_sum(A.tin.dp, sm_, om, A.tin.dp[em + q], s0, s1, s2) * rs;
-    const double tth = dt * dss_sum(A.tin.th, sm_, om, A.tin.th[em + q], s0, s1, s2) * rs;
-    const double tw = dt * dss_sum(A.tin.w, si, om, A.tin.w[ei + q], s0, s1, s2) * rs;
-    const double tph = dt * dss_sum(A.tin.phi, si, om, A.tin.phi[ei + q], s0, s1, s2) * rs;
-    const double tv1 = dt * dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2) * rs;
-    const double tv2 = dt * dss_sum(A.tin.v, sv, ov + 16, A.tin.v[ev + ov + 16 + p], s0, s1, s2) * rs;
+    const double tdp = dt * dss_sum(A.tin.dp, sm_, om, DSS_OWN(A.tin.dp[em + q]), s0, s1, s2) * rs;
+    const double tth = dt * dss_sum(A.tin.th, sm_, om, DSS_OWN(A.tin.th[em + q]), s0, s1, s2) * rs;
+    const double tw = dt * dss_sum(A.tin.w, si, om, DSS_OWN(A.tin.w[ei + q]), s0, s1, s2) * rs;
+    const double tph = dt * dss_sum(A.tin.phi, si, om, DSS_OWN(A.tin.phi[ei + q]), s0, s1, s2) * rs;
+    const double tv1 = dt * dss_sum(A.tin.v, sv, ov, DSS_OWN(A.tin.v[ev + ov + p]), s0, s1, s2) * rs;
+    const double tv2 = dt * dss_sum(A.tin.v, sv, ov + 16, DSS_OWN(A.tin.v[ev + ov + 16 + p]), s0, s1, s2) * rs;
     const double dp_old = A.st.dp[em + q];
     const double theta_old = A.th_is_theta ? A.st.th[em + q] : div_fast(A.st.th[em + q], dp_old);
     // PA:629-647 subtracts the reference state before the laplacians and adds it back afterwards; the state itself

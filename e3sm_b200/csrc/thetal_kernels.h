@@ -38,6 +38,11 @@ struct DirkArgs {
   // optional: explicit terms of state(n0) / state(nm1) saved by the CAAR launches that evaluated those states
   const double *ew_n0 = nullptr, *ephi_n0 = nullptr, *ew_nm1 = nullptr, *ephi_nm1 = nullptr;
   int *work = nullptr, *work_other = nullptr;   // element counter of this launch / of the previous one (reset here)
+  // optional: the DSS of the CAAR stage that precedes this solve, done by the DIRK kernel while it stages an element
+  // (tens.v != null): np1 = rspheremp * (node sum of tens), surface fix-up, limiter_dp3d_k, as caar_dss_post_kernel
+  StatePtrs tens{};
+  double dss_dt2 = 0.0, dss_scale1 = 0.0;
+  int dss_limiter = 0;
   int *err;
   int *max_iter;            // running max of itercount over elements (atomicMax)
   unsigned long long *max_deltaerr_bits;   // running max of deltaerr (as ordered bits)

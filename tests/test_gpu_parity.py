@@ -387,6 +387,32 @@ def test_step_is_bitwise_repeatable():
     d.close()
 
 
+@pytest.mark.parametrize("tt", [9, 10, 7])
+def test_dss_inside_the_dirk_kernel_equals_the_separate_dss_kernel(case_c1, parity_state_c1, tt):
+    """THETAL_B200_FUSE_DSS=0 restores caar_dss_post_kernel between every CAAR stage and its DIRK solve; the default
+    lets the DIRK kernel do that DSS while it stages an element.  Same arithmetic in the same order: same state."""
+    import os
+    from e3sm_b200.dycore import ThetaLDycore
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    p = p.with_(tstep_type=tt)
+    outs, launches = [], []
+    for knob in ("1", "0"):
+        os.environ["THETAL_B200_FUSE_DSS"] = knob
+        try:
+            d = ThetaLDycore(grid, hv, p, phis, gradphis, refs)
+            d.set_state(parity_state_c1.copy())
+            n_before = d.L.thetal_b200_launch_count()
+            d.prim_advance_exp(p.tstep, 0, 1, 2)
+            launches.append(d.L.thetal_b200_launch_count() - n_before)
+            outs.append(d.get_state())
+            d.close()
+        finally:
+            del os.environ["THETAL_B200_FUSE_DSS"]
+    assert launches[1] - launches[0] == (5 if tt == 7 else 4)      # one kernel less per fused stage
+    for t in (0, 1, 2):
+        assert_state_close(outs[0], outs[1], t, 1e-14, f"fused vs separate DSS, tstep_type={tt} level {t}")
+
+
 @pytest.mark.parametrize("qsplit", [1, 2])
 def test_prim_run_subcycle(case_c1, parity_state_c1, qsplit):
     """The reference entry point called as the Fortran does (prim_driver_mod.F90:554-560): four
@@ -467,6 +493,42 @@ def test_limiters_random_state(case_c1):
     o.compute_andor_apply_rhs(*args)
     d.compute_andor_apply_rhs(*args)
     assert_state_close(d.get_state(), so, 2, 1e-9, "caar on random state (limiters)")
+    d.close()
+
+
+@pytest.mark.parametrize("tt", [9, 10, 7])
+def test_one_step_with_the_dp3d_limiter_active(case_c1, parity_state_c1, tt):
+    """A physically valid state with one layer thinned to 5 % of its reference thickness inside a smooth blob (dp3d,
+    vtheta_dp and the geopotential thickness scaled together): limiter_dp3d_k (prim_advance_mod.F90:1822-1931) acts in
+    every stage of a full step, and the implicit solve runs on what it leaves.  Covers the limiter inside the DIRK
+    kernel that does the DSS of the preceding CAAR stage (dirk_col_kernel<.., DSS = true>)."""
+    from e3sm_b200.initial import make_c0
+    p, grid, hv, _, phis, gradphis, refs = case_c1
+    st = parity_state_c1.copy()
+    nlev, K = hv.nlev, 8
+    c = grid.cart.reshape(grid.nelem, 16, 3)
+    fac = 1.0 - 0.95 * np.exp(-((c - c[17, 5]) ** 2).sum(-1) / 0.15)
+    dphi = np.diff(st.phinh_i[:, 0], axis=1)
+    st.dp3d[:, 0, K] *= fac
+    st.vtheta_dp[:, 0, K] *= fac
+    dphi[:, K] *= fac
+    for k in range(nlev - 1, -1, -1):
+        st.phinh_i[:, 0, k] = st.phinh_i[:, 0, k + 1] - dphi[:, k]
+    for f in st.FIELDS:
+        a = getattr(st, f)
+        a[:, 0] = make_c0(grid, a[:, 0])
+    st.phinh_i[:, 0, nlev] = phis
+    st.set_all_timelevels(0)
+    dp0 = (hv.hyai[1:] - hv.hyai[:-1]) * hv.ps0 + (hv.hybi[1:] - hv.hybi[:-1]) * hv.ps0
+    assert (st.dp3d[:, 0, K] / dp0[K]).min() < 0.06 < p.dp3d_thresh
+    p, o, so, d = make_pair(case_c1, st, tstep_type=tt)
+    o.prim_advance_exp(p.tstep, 0, 1, 2)
+    d.prim_advance_exp(p.tstep, 0, 1, 2)
+    assert o.error_flag == 0
+    assert (so.dp3d[:, 2, K] / dp0[K]).min() > 0.12          # the limiter has refilled the layer
+    sg = d.get_state()
+    for t in (2, 0, 1):
+        assert_state_close(sg, so, t, 1e-9, f"limiter step tstep_type={tt} level {t}")
     d.close()
 
 
