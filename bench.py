@@ -320,6 +320,13 @@ def run_ours(args, world, rank, local, td):
     alg = {"caar_pre": (14 * S + 4 * Dv) / 5.0, "caar_dss_post": (10 * S + (4 * S if p.tstep_type == 9 else 0)) / 5.0,
            "dirk": (7 * S + 10 * I) / 5.0}
     nl = {"caar_pre": 5, "caar_dss_post": 5, "dirk": 5}
+    fused_dss = os.environ.get("THETAL_B200_FUSE_DSS", "1") != "0" and os.environ.get("THETAL_B200_DIRK", "1") == "1"
+    if fused_dss and p.tstep_type in (9, 10):
+        # the DSS of stages 1-4 (2S each: read the pre-DSS buffer, write the state) is done by the DIRK kernel that
+        # follows; caar_dss_post_kernel runs once per step (stage 5, with the tstep_type 9 combination behind it)
+        alg["caar_dss_post"] = 2 * S + (4 * S if p.tstep_type == 9 else 0)
+        alg["dirk"] = (7 * S + 10 * I + 8 * S) / 5.0
+        nl["caar_dss_post"] = 1
     kname = {"caar_pre": "caar_pre_kernel", "caar_dss_post": "caar_dss_post_kernel", "dirk": "dirk_col_kernel"}
     dom = max(nl, key=lambda k: fam_ms[k])
     dom_ms = fam_ms[dom] / nl[dom]
@@ -334,7 +341,8 @@ def run_ours(args, world, rank, local, td):
     roofline = {"bound": "hbm", "kernel": kname[dom], "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": traffic, "peak_kind": peak_kind,
                 "alg_bytes_per_launch": nelem * alg[dom], "launch_ms": dom_ms,
-                "note": "average over the family's 5 launches per step (the last DIRK stage also reads state(n0), state(nm1)); "
+                "note": "average over the family's launches per step (the last DIRK stage also reads state(n0), state(nm1); "
+                        "DIRK stages 1-4 include the DSS of the CAAR stage before them); "
                         "the kernel is FP64/XU-pipe bound, not HBM bound: see fp64 and profiles/r2_ncu_summary.txt",
                 "by_family": {k: {"launch_ms": fam_ms[k] / nl[k], "GBps": nelem * alg[k] / (fam_ms[k] / nl[k] * 1e-3) / 1e9,
                                   "frac": nelem * alg[k] / (fam_ms[k] / nl[k] * 1e-3) / 1e9 / peak} for k in nl}}

@@ -1503,23 +1503,41 @@ __global__ void __launch_bounds__(HV_THREADS, DSS_MINB) hv_update_kernel(const H
   }
 }
 
+// The sponge works on the top nlev_tom levels only (3 to 6 of them): a CTA takes as many elements as its 16
+// half-warps can hold at one level per half-warp (nlev_tom = 6: two elements; one element if nlev_tom > 8).
+__host__ __device__ inline int sponge_elems_per_cta(int ntom) { return ntom > 0 && ntom <= HV_THREADS / 32 ? (HV_THREADS / 16) / ntom : 1; }
+// this half-warp's element: position in the launch's element list, clamped; `mine` = it owns real work
+__device__ __forceinline__ int sponge_element(const HvArgs &A, int kslot, int ntom, int &k0, bool &mine)
+{
+  const int epc = sponge_elems_per_cta(ntom), nb = A.elist ? A.ecount : A.prm.nelem;
+  int el = 0;
+  k0 = kslot; mine = true;
+  if (epc > 1) { el = kslot / ntom; k0 = kslot - el * ntom; mine = el < epc; if (!mine) { el = epc - 1; k0 = ntom - 1; } }
+  int idx = blockIdx.x * epc + el;
+  if (idx >= nb) { idx = nb - 1; mine = false; }
+  return A.elist ? A.elist[idx] : idx;
+}
+
 // sponge pass A (PA:784-800): xfac * laplacian of the top nlev_tom levels of the state -> tout
 __global__ void __launch_bounds__(HV_THREADS, 2) hv_sponge_laplace_kernel(const HvArgs A)
 {
   extern __shared__ double smem[];
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
+  int kfirst; bool mine;
+  const int ie = sponge_element(A, kslot, ntom, kfirst, mine);
+  const int kstep = sponge_elems_per_cta(ntom) > 1 ? ntom : KS;      // several elements per CTA: one level per half-warp
   double *scr = smem + kslot * (HV_SLOTS * 16);
   Pt t; PtW w;
   pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
   ptw_init(w, t, A.geo, ie, A.prm.rearth_inv);
   const size_t em = (size_t)ie * 16 * nlev, ei = (size_t)ie * 16 * nlevp, ev = (size_t)ie * 32 * nlev;
-  const int niter = (ntom + KS - 1) / KS;
+  const int niter = (ntom + kstep - 1) / kstep;
   for (int it = 0; it < niter; it++) {
-    const int kk = it * KS + kslot;
-    const bool act = kk < ntom;
-    const int k = act ? kk : ntom - 1, q = k * 16 + p;
+    const int kk = it * kstep + kfirst;
+    const bool act = mine && kk < ntom;
+    const int k = kk < ntom ? kk : ntom - 1, q = k * 16 + p;
     double s[4], lap[4], l1, l2;
     s[0] = A.st.dp[em + q]; s[1] = A.st.th[em + q]; s[2] = A.st.w[ei + q]; s[3] = A.st.phi[ei + q];
     const double v1 = A.st.v[ev + k * 32 + p], v2 = A.st.v[ev + k * 32 + 16 + p];
@@ -1536,15 +1554,19 @@ __global__ void __launch_bounds__(HV_THREADS, 2) hv_sponge_laplace_kernel(const 
 // sponge pass B (PA:820-852): state += DSS(tin) * rspheremp on the top nlev_tom levels
 __global__ void __launch_bounds__(HV_THREADS) hv_sponge_update_kernel(const HvArgs A)
 {
-  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, ie = A.elist ? A.elist[blockIdx.x] : (int)blockIdx.x, tid = threadIdx.x;
+  const int nlev = A.prm.nlev, nlevp = nlev + 1, ntom = A.prm.nlev_tom, tid = threadIdx.x;
   const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = HV_THREADS / 16;
+  int kfirst; bool mine;
+  const int ie = sponge_element(A, kslot, ntom, kfirst, mine);
+  if (!mine) return;
+  const int kstep = sponge_elems_per_cta(ntom) > 1 ? ntom : KS;
   const int *src = A.geo.dss_src + ((size_t)ie * 16 + p) * 3;
   const int s0 = src[0], s1 = src[1], s2 = src[2];
   const double rs = A.geo.rspheremp[(size_t)ie * 16 + p];
   const size_t sm_ = 16 * (size_t)nlev, si = 16 * (size_t)nlevp, sv = 32 * (size_t)nlev;
   const size_t em = ie * sm_, ei = ie * si, ev = ie * sv;
-  for (int k = kslot; k < ntom; k += KS) {
+  for (int k = kfirst; k < ntom; k += kstep) {
     const int q = k * 16 + p;
     const size_t om = (size_t)k * 16, ov = (size_t)k * 32;
     A.st.v[ev + ov + p] += dss_sum(A.tin.v, sv, ov, A.tin.v[ev + ov + p], s0, s1, s2) * rs;
@@ -1568,8 +1590,10 @@ void launch_hv(int which, const HvArgs &A, cudaStream_t st)
       else hv_laplace2_kernel<false><<<nb, HV_THREADS, sm, st>>>(A);
       break;
     case 2: hv_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
-    case 3: hv_sponge_laplace_kernel<<<nb, HV_THREADS, sm, st>>>(A); break;
-    case 4: hv_sponge_update_kernel<<<nb, HV_THREADS, 0, st>>>(A); break;
+    case 3: { const int epc = sponge_elems_per_cta(A.prm.nlev_tom);
+              hv_sponge_laplace_kernel<<<(nb + epc - 1) / epc, HV_THREADS, sm, st>>>(A); break; }
+    case 4: { const int epc = sponge_elems_per_cta(A.prm.nlev_tom);
+              hv_sponge_update_kernel<<<(nb + epc - 1) / epc, HV_THREADS, 0, st>>>(A); break; }
   }
 }
 
