@@ -83,11 +83,23 @@ __device__ __forceinline__ void eos_level(double rth, double dphi, double &pnh, 
 // The same EOS after a Newton update that moved dphi by a small relative amount: with rth fixed,
 // pnh_new = pnh_old (dphi_old/dphi_new)^gamma, and (1 + e)^gamma is its binomial series in e = dphi_old/dphi_new - 1.
 // For |e| < 2^-4 the terms beyond degree 11 sum to less than 5e-18: the result differs from the full evaluation by
-// rounding only.  Thirteen FMAs instead of the ~65 of pow_pos.
+// rounding only; for |e| < 2^-10 the same holds for degree 4 (what remains is below 1e-17).  Thirteen or six FMAs
+// instead of the ~65 of pow_pos.  (C2: every update after the hydrostatic guess is below 2^-10.)
 #ifndef DIRK_EOS_SERIES
 #define DIRK_EOS_SERIES 1
 #endif
-constexpr double EOS_SERIES_MAX = 0.0625;
+#ifndef DIRK_EOS_SERIES_MAX
+#define DIRK_EOS_SERIES_MAX 0.0625
+#endif
+constexpr double EOS_SERIES_MAX = DIRK_EOS_SERIES_MAX, EOS_SERIES_TINY = 0.0009765625;
+__device__ __forceinline__ void eos_level_tiny_step(double e, double r, double &pnh, double &c)
+{
+  constexpr double G1 = 1.0 / (1.0 - KAPPA), G2 = G1 * (G1 - 1) / 2, G3 = G2 * (G1 - 2) / 3, G4 = G3 * (G1 - 3) / 4;
+  double s = G4;
+  s = fma(s, e, G3); s = fma(s, e, G2); s = fma(s, e, G1);
+  pnh = fma(pnh * e, s, pnh);
+  c = pnh * r;
+}
 __device__ __forceinline__ void eos_level_small_step(double e, double r, double &pnh, double &c)
 {
   constexpr double G1 = 1.0 / (1.0 - KAPPA), G2 = G1 * (G1 - 1) / 2, G3 = G2 * (G1 - 2) / 3, G4 = G3 * (G1 - 3) / 4,
@@ -633,7 +645,10 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       ee[i] = (dold[i] - dphi[i]) * rr[i];
       emax = fmax(emax, fabs(ee[i]));
     }
-    if (__all_sync(FULLMASK, emax < EOS_SERIES_MAX)) {
+    if (__all_sync(FULLMASK, emax < EOS_SERIES_TINY)) {
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) eos_level_tiny_step(ee[i], rr[i], pnh[i], cc[i]);
+    } else if (__all_sync(FULLMASK, emax < EOS_SERIES_MAX)) {
 #pragma unroll
       for (int i = 0; i < ITEMS; i++) eos_level_small_step(ee[i], rr[i], pnh[i], cc[i]);
     } else
