@@ -285,7 +285,9 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       if (dpk < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
       if (thk - A.prm.vtheta_thresh * dpk < 0) lim_th = 1;
     }
-    if (A.dss_limiter) {                    // limiter_dp3d_k: rare; block-uniform decisions
+    // one barrier in the common case: it orders the staging-area writes before the reads below and tells whether
+    // any point of the element needs limiter_dp3d_k (rare; block-uniform decisions)
+    if (__syncthreads_or(A.dss_limiter ? (lim_dp | lim_th) : 0)) {
       lim_dp = __syncthreads_or(lim_dp);
       if (lim_dp) {
         if (tid < 16) limiter_column_staged(st_dp + tid * SS, st_th + tid * SS, nlev, A.geo.spheremp[(size_t)ie * 16 + tid],
@@ -302,8 +304,8 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
           if (st_th[o] - A.prm.vtheta_thresh * st_dp[o] < 0) st_th[o] = A.prm.vtheta_thresh * st_dp[o];
         }
       }
+      __syncthreads();
     }
-    __syncthreads();
     for (int k = tid >> 4; k < nlev; k += NT / 16) {
       const int o = pt * SS + k;
       odp[(size_t)k * 16 + pt] = st_dp[o]; oth[(size_t)k * 16 + pt] = st_th[o];

@@ -42,23 +42,23 @@ void upload_hyai(const double *hyai, int nlev) { cudaMemcpyToSymbol(c_hyai, hyai
 // ------------------------------------------------------------------------------------------
 struct Pt {
   int p, a, b;
-  double da[4], db[4];          // Dvv(i,a), Dvv(i,b)
+  double da[4], db[4];          // Dvv(i,a), Dvv(i,b), times sfi = 1/rearth: ddx, ddy return derivatives per metre
   double Dinv[4], D[4];         // index b2*2+a2 of X(i,j,a2,b2)
-  double metdet, rmetdet_sfi, sfi;
+  double metdet, rmetdet, sfi;
 };
 
 __device__ __forceinline__ void pt_init(Pt &t, const Geo &g, int ie, int p, double sfi)
 {
   t.p = p; t.a = p & 3; t.b = p >> 2;
 #pragma unroll
-  for (int i = 0; i < 4; i++) { t.da[i] = c_dvv[t.a * 4 + i]; t.db[i] = c_dvv[t.b * 4 + i]; }
+  for (int i = 0; i < 4; i++) { t.da[i] = c_dvv[t.a * 4 + i] * sfi; t.db[i] = c_dvv[t.b * 4 + i] * sfi; }
 #pragma unroll
   for (int q = 0; q < 4; q++) {
     t.Dinv[q] = g.Dinv[(size_t)ie * 64 + q * 16 + p];
     t.D[q] = g.D[(size_t)ie * 64 + q * 16 + p];
   }
   t.metdet = g.metdet[(size_t)ie * 16 + p];
-  t.rmetdet_sfi = g.rmetdet[(size_t)ie * 16 + p] * sfi;
+  t.rmetdet = g.rmetdet[(size_t)ie * 16 + p];
   t.sfi = sfi;
 }
 
@@ -81,7 +81,7 @@ __device__ __forceinline__ double ddy(const Pt &t, const double *s)
 // DM:410-450
 __device__ __forceinline__ void gradient_sphere(const Pt &t, const double *s, double &g1, double &g2)
 {
-  const double v1 = ddx(t, s) * t.sfi, v2 = ddy(t, s) * t.sfi;
+  const double v1 = ddx(t, s), v2 = ddy(t, s);
   g1 = t.Dinv[0] * v1 + t.Dinv[1] * v2;
   g2 = t.Dinv[2] * v1 + t.Dinv[3] * v2;
 }
@@ -93,7 +93,7 @@ __device__ __forceinline__ void div_prep(const Pt &t, double v1, double v2, doub
 }
 __device__ __forceinline__ double div_finish(const Pt &t, const double *sgv1, const double *sgv2)
 {
-  return (ddx(t, sgv1) + ddy(t, sgv2)) * t.rmetdet_sfi;
+  return (ddx(t, sgv1) + ddy(t, sgv2)) * t.rmetdet;
 }
 // DM:915-966
 __device__ __forceinline__ void vort_prep(const Pt &t, double v1, double v2, double &vco1, double &vco2)
@@ -103,7 +103,7 @@ __device__ __forceinline__ void vort_prep(const Pt &t, double v1, double v2, dou
 }
 __device__ __forceinline__ double vort_finish(const Pt &t, const double *svco1, const double *svco2)
 {
-  return (ddx(t, svco2) - ddy(t, svco1)) * t.rmetdet_sfi;
+  return (ddx(t, svco2) - ddy(t, svco1)) * t.rmetdet;
 }
 
 // Ask the memory system to pull `bytes` (multiple of 16, 16-byte aligned) into L2 ahead of use; costs
@@ -612,6 +612,7 @@ __device__ __forceinline__ void combo9_element(const StatePtrs &a, const StatePt
       if (th - prm.vtheta_thresh * dp < 0) lim_th = 1;
     }
   }
+  if (!__syncthreads_or(lim_dp | lim_th)) return;          // common case: one barrier (block-uniform)
   lim_dp = __syncthreads_or(lim_dp);                                                // PA:324-325
   if (lim_dp) {
     __threadfence_block();
@@ -683,8 +684,8 @@ __global__ void __launch_bounds__(DSS_THREADS, DSS_MINB) caar_dss_post_kernel(co
     if (dp < A.prm.dp3d_thresh * c_dp0[k]) lim_dp = 1;
     if (th - A.prm.vtheta_thresh * dp < 0) lim_th = 1;
   }
-  if (A.do_limiter) {
-  // limiter_dp3d_k: rare; block-uniform decision
+  // limiter_dp3d_k: rare; block-uniform decisions behind one barrier in the common case
+  if (A.do_limiter && __syncthreads_or(lim_dp | lim_th)) {
   lim_dp = __syncthreads_or(lim_dp);
   if (lim_dp) {
     __threadfence_block();
@@ -1201,9 +1202,11 @@ void launch_dirk(const DirkArgs &A, cudaStream_t st)
 // Hyperviscosity (PA:546-862, VT:39-169).  Weak-form operators (DM:453-580, 784-858, 1072-1251).
 // ==========================================================================================
 struct PtW {                 // extra per-point data of the weak operators
-  double dta[4], dtb[4];     // Dvv(a,j), Dvv(b,j)
-  double mpa[4], mpb[4];     // mp(j,b) , mp(a,j)
-  double metinv[4];          // index b2*2+a2
+  double dta[4], dtb[4];     // -sfi Dvv(a,j), -sfi Dvv(b,j): the test-function derivative rows of DM:821-833 with their sign and scale
+  double ca[4], cb[4];       // sfi mp(j,b) Dvv(a,j) , sfi mp(a,j) Dvv(b,j): the level-independent factors of DM:493-503, 555-569
+  double mm[4];              // metinv (index b2*2+a2) times metdet
+  double ms[3];              // spheremp * Dinv^T Dinv (symmetric: 11, 12, 22): gradient_sphere followed by the
+                             // first half of divergence_sphere_wk (DM:410-450, 814-819) as one 2x2 product
   double spheremp;
   double lrf2;               // laplacian_rigid_factor^2
 };
@@ -1212,13 +1215,17 @@ __device__ __forceinline__ void ptw_init(PtW &w, const Pt &t, const Geo &g, int 
 {
 #pragma unroll
   for (int j = 0; j < 4; j++) {
-    w.dta[j] = c_dvv[j * 4 + t.a]; w.dtb[j] = c_dvv[j * 4 + t.b];
-    w.mpa[j] = c_mp[t.b * 4 + j]; w.mpb[j] = c_mp[j * 4 + t.a];
+    w.ca[j] = t.sfi * (c_mp[t.b * 4 + j] * c_dvv[j * 4 + t.a]); w.cb[j] = t.sfi * (c_mp[j * 4 + t.a] * c_dvv[j * 4 + t.b]);
+    w.dta[j] = -(t.sfi * c_dvv[j * 4 + t.a]); w.dtb[j] = -(t.sfi * c_dvv[j * 4 + t.b]);
   }
 #pragma unroll
-  for (int q = 0; q < 4; q++) w.metinv[q] = g.metinv[(size_t)ie * 64 + q * 16 + t.p];
+  for (int q = 0; q < 4; q++) w.mm[q] = g.metinv[(size_t)ie * 64 + q * 16 + t.p] * t.metdet;
   w.spheremp = g.spheremp[(size_t)ie * 16 + t.p];
   w.lrf2 = lrf * lrf;
+  const double sc = w.spheremp;            // ddx, ddy carry sfi
+  w.ms[0] = sc * (t.Dinv[0] * t.Dinv[0] + t.Dinv[2] * t.Dinv[2]);
+  w.ms[1] = sc * (t.Dinv[0] * t.Dinv[1] + t.Dinv[2] * t.Dinv[3]);
+  w.ms[2] = sc * (t.Dinv[1] * t.Dinv[1] + t.Dinv[3] * t.Dinv[3]);
 }
 
 constexpr int HV_THREADS = 256;
@@ -1244,11 +1251,10 @@ __device__ __forceinline__ void laplace_level(const Pt &t, const PtW &w, double 
   __syncwarp();
 #pragma unroll
   for (int f = 0; f < 4; f++) {
-    double g1, g2;
-    gradient_sphere(t, scr + f * 16, g1, g2);
-    // divergence_sphere_wk first half DM:814-819, times spheremp
-    scr[(8 + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[0] * g1 + t.Dinv[2] * g2);
-    scr[(9 + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[1] * g1 + t.Dinv[3] * g2);
+    // gradient_sphere, then divergence_sphere_wk first half (DM:814-819) times spheremp: one symmetric 2x2 product
+    const double dx = ddx(t, scr + f * 16), dy = ddy(t, scr + f * 16);
+    scr[(8 + 2 * f) * 16 + p] = w.ms[0] * dx + w.ms[1] * dy;
+    scr[(9 + 2 * f) * 16 + p] = w.ms[1] * dx + w.ms[2] * dy;
   }
   const double div = nu_ratio * div_finish(t, scr + 4 * 16, scr + 5 * 16);
   const double vor = vort_finish(t, scr + 6 * 16, scr + 7 * 16);
@@ -1260,26 +1266,27 @@ __device__ __forceinline__ void laplace_level(const Pt &t, const PtW &w, double 
     const double *T1 = scr + (8 + 2 * f) * 16 + t.b * 4, *T2 = scr + (9 + 2 * f) * 16 + t.a;
     double acc = 0.0;
 #pragma unroll
-    for (int j = 0; j < 4; j++) acc = acc - (T1[j] * w.dta[j] + T2[4 * j] * w.dtb[j]) * t.sfi;
+    for (int j = 0; j < 4; j++) acc = fma(T1[j], w.dta[j], fma(T2[4 * j], w.dtb[j], acc));
     lap_s[f] = acc;
   }
   {
     const double *sd_r = scr + 16 * 16 + t.b * 4, *sd_c = scr + 16 * 16 + t.a;      // div(j,b), div(a,j)
     const double *sv_r = scr + 17 * 16 + t.b * 4, *sv_c = scr + 17 * 16 + t.a;
-    double gc1 = 0.0, gc2 = 0.0, cc1 = 0.0, cc2 = 0.0;
+    // gradient_sphere_wk_testcov (DM:555-569) and curl_sphere_wk_testcov (DM:493-503): the products of mp, Dvv,
+    // metinv and metdet do not depend on the level, so each of the four sums over j is taken once with the
+    // combined factors (the reference multiplies them out inside the sum: same value up to rounding)
+    double sa = 0.0, sb = 0.0, va = 0.0, vb = 0.0;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      // gradient_sphere_wk_testcov DM:555-569
-      gc1 = gc1 - ((w.mpa[j] * w.metinv[0] * t.metdet * sd_r[j] * w.dta[j]) + (w.mpb[j] * w.metinv[1] * t.metdet * sd_c[4 * j] * w.dtb[j]));
-      gc2 = gc2 - ((w.mpa[j] * w.metinv[2] * t.metdet * sd_r[j] * w.dta[j]) + (w.mpb[j] * w.metinv[3] * t.metdet * sd_c[4 * j] * w.dtb[j]));
-      // curl_sphere_wk_testcov DM:493-503
-      cc1 = cc1 - (w.mpb[j] * sv_c[4 * j] * w.dtb[j]);
-      cc2 = cc2 + (w.mpa[j] * sv_r[j] * w.dta[j]);
+      sa = fma(w.ca[j], sd_r[j], sa); sb = fma(w.cb[j], sd_c[4 * j], sb);
+      va = fma(w.ca[j], sv_r[j], va); vb = fma(w.cb[j], sv_c[4 * j], vb);
     }
-    const double gr1 = (t.D[0] * gc1 + t.D[2] * gc2) * t.sfi, gr2 = (t.D[1] * gc1 + t.D[3] * gc2) * t.sfi;
-    const double cu1 = (t.D[0] * cc1 + t.D[2] * cc2) * t.sfi, cu2 = (t.D[1] * cc1 + t.D[3] * cc2) * t.sfi;
-    lap_v1 = (gr1 - cu1) + 2 * w.spheremp * v1 * w.lrf2;                              // DM:1241-1247
-    lap_v2 = (gr2 - cu2) + 2 * w.spheremp * v2 * w.lrf2;
+    const double gc1 = -(w.mm[0] * sa + w.mm[1] * sb), gc2 = -(w.mm[2] * sa + w.mm[3] * sb);
+    const double cc1 = -vb, cc2 = va;
+    // covariant -> lat-lon of (grad - curl) in one product, DM:1241-1247
+    const double d1 = gc1 - cc1, d2 = gc2 - cc2;
+    lap_v1 = (t.D[0] * d1 + t.D[2] * d2) + 2 * w.spheremp * v1 * w.lrf2;
+    lap_v2 = (t.D[1] * d1 + t.D[3] * d2) + 2 * w.spheremp * v2 * w.lrf2;
   }
   __syncwarp();
 }
@@ -1298,15 +1305,19 @@ __device__ __forceinline__ void laplace_scalars(const Pt &t, const PtW &w, const
   __syncwarp();
 #pragma unroll
   for (int f = 0; f < NF; f++) {
-    double g1, g2;
-    gradient_sphere(t, scr + f * 16, g1, g2);
     if (TENSOR) {
+      double g1, g2;
+      gradient_sphere(t, scr + f * 16, g1, g2);
       const double o1 = g1, o2 = g2;
       g1 = o1 * tv[0] + o2 * tv[2];
       g2 = o1 * tv[1] + o2 * tv[3];
+      scr[(NF + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[0] * g1 + t.Dinv[2] * g2);      // DM:814-819
+      scr[(NF + 2 * f + 1) * 16 + p] = w.spheremp * (t.Dinv[1] * g1 + t.Dinv[3] * g2);
+    } else {
+      const double dx = ddx(t, scr + f * 16), dy = ddy(t, scr + f * 16);
+      scr[(NF + 2 * f) * 16 + p] = w.ms[0] * dx + w.ms[1] * dy;
+      scr[(NF + 2 * f + 1) * 16 + p] = w.ms[1] * dx + w.ms[2] * dy;
     }
-    scr[(NF + 2 * f) * 16 + p] = w.spheremp * (t.Dinv[0] * g1 + t.Dinv[2] * g2);      // DM:814-819
-    scr[(NF + 2 * f + 1) * 16 + p] = w.spheremp * (t.Dinv[1] * g1 + t.Dinv[3] * g2);
   }
   __syncwarp();
 #pragma unroll
@@ -1314,7 +1325,7 @@ __device__ __forceinline__ void laplace_scalars(const Pt &t, const PtW &w, const
     const double *T1 = scr + (NF + 2 * f) * 16 + t.b * 4, *T2 = scr + (NF + 2 * f + 1) * 16 + t.a;
     double acc = 0.0;
 #pragma unroll
-    for (int j = 0; j < 4; j++) acc = acc - (T1[j] * w.dta[j] + T2[4 * j] * w.dtb[j]) * t.sfi;
+    for (int j = 0; j < 4; j++) acc = fma(T1[j], w.dta[j], fma(T2[4 * j], w.dtb[j], acc));
     lap_s[f] = acc;
   }
   __syncwarp();
