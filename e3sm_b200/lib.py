@@ -31,12 +31,31 @@ SYMBOLS = [
 ]
 
 
+def _preload_bundled_nccl():
+    """The library links against libnccl.so.2; PyTorch ships its own copy under the same soname and needs the symbols of
+    that version.  Whichever copy a process loads first serves both, so when a PyTorch-bundled NCCL is installed it is
+    loaded (globally) before the library: `import torch` keeps working whatever the import order.  A Fortran host
+    without Python is not concerned: there the system NCCL is the only one."""
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+                return path
+    except Exception:
+        pass
+    return None
+
+
 def load():
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
                                "(there is no CPU fallback)")
+        _preload_bundled_nccl()
         _lib = ctypes.CDLL(LIB_PATH)
         _lib.thetal_b200_last_error.restype = ctypes.c_int
         _lib.thetal_b200_last_error_msg.restype = ctypes.c_char_p

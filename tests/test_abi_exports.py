@@ -1,6 +1,5 @@
 """The drop-in boundary without a GPU: libthetal_b200.so loads and exports every entry point that
 include/thetal_b200.h declares, and e3sm_b200/lib.py lists the same set.  No compute call is made."""
-import ctypes
 import os
 import re
 import subprocess
@@ -28,7 +27,7 @@ def library():
     from e3sm_b200 import lib
     if not os.path.exists(lib.LIB_PATH):
         subprocess.run(["make", "-C", os.path.dirname(lib.LIB_PATH)], check=True, capture_output=True)
-    return ctypes.CDLL(lib.LIB_PATH)
+    return lib.load()          # the product's own loader (it orders the NCCL copies, see lib._preload_bundled_nccl)
 
 
 def test_header_declares_entry_points():
@@ -48,3 +47,13 @@ def test_library_exports_every_declared_symbol():
 def test_loader_lists_the_header():
     from e3sm_b200 import lib
     assert sorted(lib.SYMBOLS) == sorted(declared_symbols())
+
+
+def test_torch_imports_after_the_library():
+    """The library and PyTorch share the soname libnccl.so.2: loading the library first must not break `import torch`
+    (a fresh interpreter, library first)."""
+    import sys
+    code = ("import sys; sys.path.insert(0, %r); from e3sm_b200 import lib; lib.load(); import torch; "
+            "import torch.distributed; print('ok')" % ROOT)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
