@@ -228,6 +228,13 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     bulk_g2s(sw, A.n0.w + (size_t)ie * 16 * nlevp, bi, &stage_bar);
     bulk_g2s(sphi, A.n0.phi + (size_t)ie * 16 * nlevp, bi, &stage_bar);
   }
+  // the per-point geometry of phase 2 is requested while the bulk copies are in flight (its latency would otherwise
+  // be paid after the EOS phase, with nothing to overlap it)
+  const int p = tid & 15, kslot = tid >> 4;
+  Pt t;
+  pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
+  const double fcor = A.geo.fcor[(size_t)ie * 16 + p], spheremp = A.geo.spheremp[(size_t)ie * 16 + p];
+  const double gps1 = A.geo.gradphis[(size_t)ie * 32 + p], gps2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
   mbar_wait(&stage_bar, 0);
   // ---- phase 1: EOS (EOS:175-183), one pow per point-level ----
   {
@@ -246,10 +253,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   __syncthreads();
 
   // ---- phase 2: tendencies, a half-warp per level ----
-  const int p = tid & 15, kslot = tid >> 4;
   constexpr int KS = CAAR_THREADS / 16;
-  Pt t;
-  pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
   if (VADV) {
     // eta_dot_dpdn at the interfaces (PA:1227-1251) needs the divergence of every level first
     for (int k = kslot; k < ((nlev + KS - 1) / KS) * KS; k += KS) {
@@ -272,8 +276,6 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     }
     __syncthreads();
   }
-  const double fcor = A.geo.fcor[(size_t)ie * 16 + p], spheremp = A.geo.spheremp[(size_t)ie * 16 + p];
-  const double gps1 = A.geo.gradphis[(size_t)ie * 32 + p], gps2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
   const double s1 = A.scale1, s2 = A.scale2, s3 = A.scale3, dt2 = A.dt2;
   constexpr bool accum = ACCUM;
   const int niter = (nlev + KS - 1) / KS;
