@@ -130,6 +130,10 @@ __device__ __forceinline__ void cp_async8(double *dst, const double *src)
 {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
+__device__ __forceinline__ void cp_async4(int *dst, const int *src)
+{
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -174,6 +178,9 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   extern __shared__ double smem[];
   __shared__ double red[3][NW];
   __shared__ int sflag;
+  // DSS: the gather table entries and 1/mass of this thread's point, fetched with the element's columns (one element ahead)
+  __shared__ int s_src[DSS ? 3 : 1][DSS ? NT : 1];
+  __shared__ double s_rs[DSS ? NT : 1];
   const int nlev = A.prm.nlev, nlevp = nlev + 1, n16 = 16 * nlev, nelem = A.prm.nelem;
   const int tid = threadIdx.x, j = tid % TPC, p = tid / TPC, k0 = j * ITEMS;
   double *s_w0 = smem + tid, *s_dphi0 = smem + ITEMS * NT + tid, *s_phi0 = smem + 2 * ITEMS * NT + tid;
@@ -202,6 +209,11 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
     for (int q = tid; q < 2 * n16; q += NT) {
       const int o = (q & 15) * SS + (q >> 5);
       cp_async8(((q & 16) ? st_v2 : st_v1) + o, ev + q);
+    }
+    if constexpr (DSS) {
+      const int *src = A.geo.dss_src + ((size_t)e * 16 + (tid & 15)) * 3;
+      cp_async4(&s_src[0][tid], src); cp_async4(&s_src[1][tid], src + 1); cp_async4(&s_src[2][tid], src + 2);
+      cp_async8(&s_rs[tid], A.geo.rspheremp + (size_t)e * 16 + (tid & 15));
     }
     cp_async_commit();
   };
@@ -250,10 +262,12 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
   if constexpr (DSS) {
     // ---- DSS and post-processing of the CAAR stage (PA:1741-1772, 1812-1931), [level][point] over the threads ----
     const int pt = tid & 15;
-    const int *src = A.geo.dss_src + ((size_t)ie * 16 + pt) * 3;
-    const int s0 = src[0], s1 = src[1], s2 = src[2];
-    const double rs = A.geo.rspheremp[(size_t)ie * 16 + pt];
+    const int s0 = s_src[0][tid], s1 = s_src[1][tid], s2 = s_src[2][tid];
+    const double rs = s_rs[tid];
     const size_t ev = 2 * (size_t)n16, em = (size_t)n16, ei = 16 * (size_t)nlevp;
+    // surface data of the fix-up below: requested now so that the warp that owns level nlev does not wait for them
+    const double g1 = A.geo.gradphis[(size_t)ie * 32 + pt], g2 = A.geo.gradphis[(size_t)ie * 32 + 16 + pt];
+    const double phis_pt = A.np1.phi[(size_t)ie * ei + (size_t)nlev * 16 + pt];   // phinh_i(nlevp) = phis: every time level holds it
     double *ov = A.np1.v + (size_t)ie * ev, *odp = A.np1.dp + (size_t)ie * em, *oth = A.np1.th + (size_t)ie * em;
     int lim_dp = 0, lim_th = 0;
     for (int k = tid >> 4; k < nlev; k += NT / 16) {
@@ -271,14 +285,13 @@ __global__ void __launch_bounds__(16 * TPC, (DirkColCfg<ITEMS, TPC>::minb)) dirk
       if (k == nlev - 1) {                                                            // PA:1751-1772
         const size_t ob = (size_t)nlev * 16;
         double wb = rs * dss_sum(A.tens.w, ei, ob, st_w[o + 1], s0, s1, s2);
-        const double g1 = A.geo.gradphis[(size_t)ie * 32 + pt], g2 = A.geo.gradphis[(size_t)ie * 32 + 16 + pt];
         const double dpnh = 1 + (((v1 * g1 + v2 * g2) / G_GRAV - wb) / (G_GRAV + (g1 * g1 + g2 * g2) / (2 * G_GRAV))) / A.dss_dt2;
         wb = wb + A.dss_scale1 * A.dss_dt2 * G_GRAV * (dpnh - 1);
         v1 = v1 - A.dss_scale1 * A.dss_dt2 * (dpnh - 1) * g1 / 2;
         v2 = v2 - A.dss_scale1 * A.dss_dt2 * (dpnh - 1) * g2 / 2;
         st_w[o + 1] = wb;
         A.np1.w[(size_t)ie * ei + ob + pt] = wb;
-        st_phi[o + 1] = A.np1.phi[(size_t)ie * ei + ob + pt];      // phinh_i(nlevp) = phis: every time level holds it
+        st_phi[o + 1] = phis_pt;
       }
       st_v1[o] = v1; st_v2[o] = v2;
       ov[offv + pt] = v1; ov[offv + 16 + pt] = v2;
