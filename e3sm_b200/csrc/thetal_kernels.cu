@@ -216,17 +216,19 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   }
   // ---- phase 0: stage the n0 columns of this element: five TMA bulk copies (each field of an
   // element is one contiguous block), completion counted in bytes on an mbarrier ----
-  __shared__ unsigned long long stage_bar;
-  if (tid == 0) mbar_init(&stage_bar, 1);
+  // two barriers: the EOS phase needs vtheta_dp, dp3d and phinh_i only and starts while v and w_i still travel
+  __shared__ unsigned long long stage_bar[2];
+  if (tid == 0) { mbar_init(&stage_bar[0], 1); mbar_init(&stage_bar[1], 1); }
   __syncthreads();
   if (tid == 0) {
     const unsigned bv = 32u * nlev * 8u, bm = 16u * nlev * 8u, bi = 16u * nlevp * 8u;
-    mbar_expect_tx(&stage_bar, bv + 2 * bm + 2 * bi);
-    bulk_g2s(sv, A.n0.v + (size_t)ie * 32 * nlev, bv, &stage_bar);
-    bulk_g2s(sdp, A.n0.dp + (size_t)ie * 16 * nlev, bm, &stage_bar);
-    bulk_g2s(sth, A.n0.th + (size_t)ie * 16 * nlev, bm, &stage_bar);
-    bulk_g2s(sw, A.n0.w + (size_t)ie * 16 * nlevp, bi, &stage_bar);
-    bulk_g2s(sphi, A.n0.phi + (size_t)ie * 16 * nlevp, bi, &stage_bar);
+    mbar_expect_tx(&stage_bar[0], 2 * bm + bi);
+    bulk_g2s(sth, A.n0.th + (size_t)ie * 16 * nlev, bm, &stage_bar[0]);
+    bulk_g2s(sphi, A.n0.phi + (size_t)ie * 16 * nlevp, bi, &stage_bar[0]);
+    bulk_g2s(sdp, A.n0.dp + (size_t)ie * 16 * nlev, bm, &stage_bar[0]);
+    mbar_expect_tx(&stage_bar[1], bv + bi);
+    bulk_g2s(sv, A.n0.v + (size_t)ie * 32 * nlev, bv, &stage_bar[1]);
+    bulk_g2s(sw, A.n0.w + (size_t)ie * 16 * nlevp, bi, &stage_bar[1]);
   }
   // the per-point geometry of phase 2 is requested while the bulk copies are in flight (its latency would otherwise
   // be paid after the EOS phase, with nothing to overlap it)
@@ -235,7 +237,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
   pt_init(t, A.geo, ie, p, A.prm.rearth_inv);
   const double fcor = A.geo.fcor[(size_t)ie * 16 + p], spheremp = A.geo.spheremp[(size_t)ie * 16 + p];
   const double gps1 = A.geo.gradphis[(size_t)ie * 32 + p], gps2 = A.geo.gradphis[(size_t)ie * 32 + 16 + p];
-  mbar_wait(&stage_bar, 0);
+  mbar_wait(&stage_bar[0], 0);
   // ---- phase 1: EOS (EOS:175-183), one pow per point-level ----
   {
     int bad = 0;
@@ -250,6 +252,7 @@ __global__ void __launch_bounds__(CAAR_THREADS, 2) caar_pre_kernel(const CaarArg
     }
     if (bad) atomicOr(A.err, ERR_EOS_BAD_STATE);
   }
+  mbar_wait(&stage_bar[1], 0);
   __syncthreads();
 
   // ---- phase 2: tendencies, a half-warp per level ----
