@@ -13,6 +13,10 @@
 //   3. every lane back-substitutes its interior unknowns (two FMAs per row).
 // Levels beyond nlev (the column is padded to TPC*ITEMS rows) are identity rows behind the last real
 // row, whose super-diagonal is zero, so they never couple to anything.
+// The EOS of IM:261 and IM:324 is evaluated without pow wherever that is exact to rounding (eos_level_*_step below:
+// binomial series in the relative change of dphi; the hydrostatic guess returns the hydrostatic pressure).
+// With DSS = true the kernel also finishes the CAAR stage before it (node sum, rspheremp, surface fix-up,
+// limiter_dp3d_k: PA:1741-1772, 1812-1931) on the staged columns and writes all six prognostics of np1.
 // Included by thetal_kernels.cu inside namespace thetal (uses its constants and helpers).
 #pragma once
 
