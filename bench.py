@@ -521,6 +521,15 @@ def main():
     ap.add_argument("--no-strong", dest="strong", action="store_false",
                     help="skip the C3 strong-scaling block of the default N>1 run")
     args = ap.parse_args()
+    if args.impl == "reference":
+        # CPU arm: no process group and no GPU context; under torchrun rank 0 alone runs it, the others exit 0 at once
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
+        if args.config is None:
+            args.config = "C2"
+        args.steps = min(args.steps, 5)     # bounded sample: each step is ~0.5 s of CPU work on 16 cores
+        run_reference(args, int(os.environ.get("WORLD_SIZE", "1")), 0, None)
+        return
     world, rank, local, td = dist_setup(args.gpus)
     args.weak_ne = 0
     if args.config is None:
@@ -529,12 +538,7 @@ def main():
             args.weak_ne = int(round(30.0 * world ** 0.5))      # 2: ne42, 4: ne60, 8: ne85
     else:
         args.strong = False
-    if args.impl == "reference":
-        if args.steps > 5:
-            args.steps = 5          # bounded sample: each step is ~0.5 s of CPU work on 16 cores
-        run_reference(args, world, rank, td)
-    else:
-        run_ours(args, world, rank, local, td)
+    run_ours(args, world, rank, local, td)
     if td is not None:
         td.destroy_process_group()
 
