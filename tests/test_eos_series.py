@@ -58,3 +58,26 @@ def test_degree_4_is_not_enough_at_the_upper_threshold():
     """the tiers are needed: degree 4 at |e| = 2^-4 misses by 1e-9"""
     e = np.array([2.0 ** -4])
     assert abs(series(e, 4)[0] / exact(e)[0] - 1.0) > 1e-10
+
+
+def test_eos_at_the_hydrostatic_guess_returns_the_hydrostatic_pressure(case_c1):
+    """IM:228-230 builds the Newton guess with phi_from_eos (EOS:286-302), the inverse of the EOS (EOS:175-183) at the
+    hydrostatic mid-level pressure; the kernel therefore takes pnh = pmid at the guess instead of evaluating the EOS
+    (IM:261).  What is neglected is the rounding of the interface sums: measured here on the JW state of C1."""
+    p, grid, hv, st, phis, gradphis, refs = case_c1
+    P0 = 1.0e5
+    kappa = RGAS / CP
+    dp, th = st.dp3d[:, 0], st.vtheta_dp[:, 0]                       # [e, nlev, 16]
+    nlev = hv.nlev
+    ptop = hv.hyai[0] * hv.ps0
+    pint = ptop + np.concatenate([np.zeros_like(dp[:, :1]), np.cumsum(dp, axis=1)], axis=1)
+    pmid = (pint[:, 1:] + pint[:, :-1]) / 2
+    term = RGAS * th * (pmid / P0) ** (kappa - 1.0) / P0           # -dphi of the guess
+    phi = np.empty((dp.shape[0], nlev + 1, 16))
+    phi[:, nlev] = phis
+    for k in range(nlev - 1, -1, -1):
+        phi[:, k] = phi[:, k + 1] + term[:, k]
+    dphi = phi[:, 1:] - phi[:, :-1]                                  # what the Newton iteration starts from
+    pnh = P0 * (RGAS * th / (-dphi) / P0) ** (1.0 / (1.0 - kappa))
+    rel = np.abs(pnh / pmid - 1.0).max()
+    assert rel <= 2e-14, rel          # measured 2.4e-15 (L26), 4.7e-15 (L72)
